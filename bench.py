@@ -1,0 +1,401 @@
+#!/usr/bin/env python
+"""bench.py -- DLRM embedding-bag samples/sec fwd+bwd (+ sparse SGD) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config C3] [--dist uniform|zipf --alpha A]
+    python bench.py --impl reference ...      # the reference's CPU path on the host cores
+
+A "step" is one pass of the hot path over one batch of synthetic input:
+forward gather-and-pool of every table, then the deterministic backward (key
+build + sort) and the sparse SGD update of the touched rows.  Prints ONE JSON
+line (rank 0).  `value` times the step with inputs resident in HBM; `e2e`
+times the same step driven from pinned HOST buffers through the public API
+(H2D indices + upstream gradients, D2H pooled outputs inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "DLRM embedding-bag samples/sec fwd+bwd"
+UNIT = "samples/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C3", help="workload: C1..C5 (dlrm_flexflow_b200/workloads.py)")
+    ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf"])
+    ap.add_argument("--alpha", type=float, default=0.0)
+    ap.add_argument("--pool", type=int, default=8, help="pre-generated index batches to rotate through")
+    ap.add_argument("--lr", type=float, default=0.01)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-row-cap", type=int, default=2_000_000)
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    return ap.parse_args()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------
+# clocks during the timed region
+# ---------------------------------------------------------------------------
+class ClockSampler(object):
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# CPU leg: the reference's own CPU embedding arithmetic on the host cores.
+# The only place outside tests/ and smoke() that executes oracle/.
+# ---------------------------------------------------------------------------
+def cpu_reference_run(w, steps, warmup, row_cap, lr):
+    import numpy as np
+    import psutil
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle as O
+
+    D, B, L, aggr = w["dim"], w["batch"], w["bag"], w["aggr"]
+    avail = psutil.virtual_memory().available
+    rows = [min(r, row_cap) for r in w["rows"]]
+    while sum(rows) * D * 4 * 2 > 0.4 * avail and row_cap > 1000:   # tables + gradient scratch
+        row_cap //= 2
+        rows = [min(r, row_cap) for r in w["rows"]]
+    T = len(rows)
+    cores = min(os.cpu_count() or 1, T)
+    rng = np.random.default_rng(1234)
+    Ws, Gs, idxs, gs, outs = [], [], [], [], []
+    for t, n in enumerate(rows):
+        r = np.float32((1.0 / n) ** 0.5)
+        Ws.append(O.uniform_init(n * D, 1234 + t, -r, r).reshape(n, D))
+        Gs.append(np.zeros((n, D), np.float32))
+        idxs.append(rng.integers(0, n, size=(B, L)).astype(np.int64))
+        gs.append(rng.standard_normal((B, D), dtype=np.float32))
+        outs.append(np.empty((B, D), np.float32))
+    use_ref = O.have_ref()
+    lengths = np.full(B, L, np.int32)
+    L_ = O.lib()
+    fp, ip = O._fp, O._ip
+
+    def one_table(t):
+        if use_ref:   # the reference's AVX2 kernel itself (src/ops/embedding_avx2.cc:5-296)
+            O.ref()(D, B, B * L, rows[t], fp(Ws[t]), ip(idxs[t]), lengths.ctypes.data_as(O._i32p), None,
+                    bool(aggr == O.AGGR_MODE_AVG), fp(outs[t]))
+        else:
+            L_.ffo_embed_forward(D, B, rows[t], fp(Ws[t]), ip(idxs[t]), None, L,
+                                 int(aggr == O.AGGR_MODE_AVG), fp(outs[t]), D)
+        L_.ffo_embed_backward_sgd_touched(D, B, rows[t], ip(idxs[t]), L, aggr, fp(gs[t]), D, lr,
+                                          fp(Gs[t]), fp(Ws[t]))
+
+    pool = ThreadPoolExecutor(max_workers=cores)
+    # biggest tables first so the tail of the step is short
+    order = sorted(range(T), key=lambda t: -rows[t])
+
+    def step():
+        list(pool.map(one_table, order))
+
+    for _ in range(max(warmup, 1)):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    pool.shutdown()
+    sample = ("%s with every table capped at %d rows (%.1f GB of tables in host RAM), full batch %d, "
+              "%d steps; forward = %s, backward + SGD = C restatement of embedding.cc:54-72 / "
+              "optimizer_kernel.cu:23-41 on touched rows only (the reference's dense zero + dense "
+              "sgd_update are NOT charged); %d threads, one table per thread"
+              % (w["name"], row_cap, sum(rows) * D * 4 / 1e9, B, steps,
+                 "the reference's own AVX2 kernel (oracle/_ref)" if use_ref else "C restatement (oracle port)",
+                 cores))
+    return {"value": B / dt, "unit": UNIT, "cores": cores, "kind": "reference" if use_ref else "port",
+            "sample": sample, "ms_per_step": dt * 1e3}
+
+
+def run_reference_arm(args, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb = cpu_reference_run(w, max(args.steps, 1), max(args.warmup, 1), args.cpu_row_cap, args.lr)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": workload_config(args, w, 1),
+        "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, w, world):
+    return {"workload": "%s: %s" % (w["name"], w["desc"]), "tables": len(w["rows"]), "out_dim": w["dim"],
+            "bag_size": w["bag"], "aggr": "AVG" if w["aggr"] == 22 else "SUM", "global_batch": w["batch"],
+            "index_dist": args.dist if args.dist == "uniform" else "zipf(alpha=%g)" % args.alpha,
+            "table_bytes": sum(w["rows"]) * w["dim"] * 4, "optimizer": "SGD lr=%g wd=0 momentum=0" % args.lr,
+            "parallelism": "table-wise x%d" % world if world > 1 else "single GPU",
+            "l2_policy": "inputs_larger_than_l2" if w["working_set"] > 2 * 126e6 else "l2_flush_between_steps"}
+
+
+# ---------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------
+def run_ours(args, w):
+    import torch
+    import dlrm_flexflow_b200 as ff
+    from dlrm_flexflow_b200 import kernels, workloads
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torchrun --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if world > 1:
+        raise SystemExit("multi-GPU bench not wired yet")
+
+    D, B, L, aggr = w["dim"], w["batch"], w["bag"], w["aggr"]
+    rows = w["rows"]
+    T = len(rows)
+    stream = torch.cuda.current_stream()
+
+    cfg = ff.FFConfig()
+    cfg.set_batch_size(B)
+    cfg.set_rank(0, local_rank)
+    m = ff.FFModel(cfg)
+    m.set_stream(stream.cuda_stream)
+    ins, outs = [], []
+    for t in range(T):
+        x = m.create_tensor([B, L], ff.DataType.DT_INT64)
+        r = (1.0 / rows[t]) ** 0.5      # DLRM's range, examples/cpp/DLRM/dlrm.cc:44
+        outs.append(m.embedding(x, rows[t], D, ff.AggrMode(aggr), None, ff.UniformInitializer(1234 + t, -r, r)))
+        ins.append(x)
+    m.compile(optimizer=ff.SGDOptimizer(m, args.lr))
+    m.init_layers()
+
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(4321)
+    pool = torch.empty((args.pool, T, B, L), dtype=torch.int64, device="cuda")
+    for p in range(args.pool):
+        for t in range(T):
+            pool[p, t] = workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen)
+    out = torch.empty((B, T * D), device="cuda")
+    grad = torch.randn((B, T * D), device="cuda", generator=gen)
+    for t in range(T):
+        outs[t].attach_torch(out[:, t * D:(t + 1) * D])
+        outs[t].attach_torch(grad[:, t * D:(t + 1) * D], grad=True)
+    # unique (table,row) pairs per batch: the rows the update reads and writes
+    uniq = []
+    for p in range(args.pool):
+        u = 0
+        for t in range(T):
+            u += int(torch.unique(pool[p, t]).numel())
+        uniq.append(u)
+    n_lookups = T * B * L
+
+    flush = None
+    if w["working_set"] <= 2 * 126e6:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def step(p, ev=None):
+        for t in range(T):
+            ins[t].attach_torch(pool[p, t])
+        if ev:
+            ev[0].record()
+        m.forward()
+        if ev:
+            ev[1].record()
+        m.zero_gradients()
+        m.backward()
+        if ev:
+            ev[2].record()
+        m.update()
+        if ev:
+            ev[3].record()
+
+    for i in range(max(args.warmup, 3)):
+        step(i % args.pool)
+        if flush is not None:
+            flush.zero_()
+    m.sync()
+
+    K = args.steps
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = kernels.kernel_launch_count()
+    torch.cuda.synchronize()
+    for i in range(K):
+        step((args.warmup + i) % args.pool, evs[i])
+        if flush is not None:
+            flush.zero_()
+    torch.cuda.synchronize()
+    launches = kernels.kernel_launch_count() - launches0
+    clocks = sampler.stop()
+    m.sync()   # surfaces an out-of-range index as an error
+
+    if flush is None:
+        total_ms = evs[0][0].elapsed_time(evs[-1][3])
+    else:
+        total_ms = sum(e[0].elapsed_time(e[3]) for e in evs)
+    ms_step = total_ms / K
+    fwd_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / K
+    sort_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / K
+    upd_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / K
+    U = sum(uniq[(args.warmup + i) % args.pool] for i in range(K)) / K
+
+    peak, peak_src = measured_peaks()
+    fwd_bytes = n_lookups * D * 4                  # rows gathered
+    upd_bytes = 2 * U * D * 4                      # touched rows read + written
+    step_bytes = fwd_bytes + upd_bytes
+    phases = {
+        "forward": {"ms": fwd_ms, "algorithmic_bytes": fwd_bytes, "gbs": fwd_bytes / fwd_ms / 1e6,
+                    "full_bytes": fwd_bytes * 2 + n_lookups * 8},
+        "backward_sort": {"ms": sort_ms, "algorithmic_bytes": 0, "keys": n_lookups},
+        "sgd_update": {"ms": upd_ms, "algorithmic_bytes": upd_bytes, "gbs": upd_bytes / upd_ms / 1e6,
+                       "full_bytes": upd_bytes + n_lookups * D * 4 + n_lookups * 8},
+    }
+    dom = "sgd_update" if upd_ms >= fwd_ms else "forward"
+    roofline = {"bound": "hbm", "kernel": "reduce_l1_kernel (segment reduce + sparse SGD)" if dom == "sgd_update"
+                else "fwd_onehot/multihot_kernel (gather-and-pool)",
+                "achieved": phases[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": phases[dom]["gbs"] / peak, "peak_source": peak_src, "traffic": None,
+                "achieved_full": phases[dom]["full_bytes"] / phases[dom]["ms"] / 1e6}
+    line = {
+        "metric": METRIC, "value": B / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, w, world),
+        "roofline": roofline,
+        "step_roofline": {"algorithmic_bytes": step_bytes, "unique_rows": U, "lookups": n_lookups,
+                          "gbs": step_bytes / ms_step / 1e6, "frac_of_measured_peak": step_bytes / ms_step / 1e6 / peak,
+                          "frac_of_8tbs_nominal": step_bytes / ms_step / 1e6 / 8000.0},
+        "phases": phases, "clocks": clocks, "gpu_launches": int(launches),
+    }
+
+    # ---- end to end: host buffers in, host buffers out, through the public API
+    if not args.no_e2e:
+        idx_host = pool[0].cpu().pin_memory()
+        grad_host = torch.empty((B, T * D), pin_memory=True)
+        grad_host.copy_(grad)
+        out_host = torch.empty((B, T * D), pin_memory=True)
+        idx_dev = torch.empty_like(pool[0])
+        for t in range(T):
+            ins[t].attach_torch(idx_dev[t])
+
+        def e2e_step():
+            idx_dev.copy_(idx_host, non_blocking=True)
+            m.forward()
+            out_host.copy_(out, non_blocking=True)
+            grad.copy_(grad_host, non_blocking=True)
+            m.zero_gradients()
+            m.backward()
+            m.update()
+            torch.cuda.synchronize()       # the host now owns this step's pooled output
+
+        for _ in range(2):
+            e2e_step()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(args.e2e_steps):
+            e2e_step()
+        e.record()
+        torch.cuda.synchronize()
+        e2e_ms = s.elapsed_time(e) / args.e2e_steps
+        line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                       "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
+                       "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps}
+        m.sync()
+        del idx_host, grad_host, out_host
+
+    if not args.no_cpu_baseline and rank == 0 and world == 1:
+        cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
+        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    from dlrm_flexflow_b200 import workloads
+    w = dict(workloads.WORKLOADS[args.config])
+    w["name"] = args.config
+    n = len(w["rows"]) * w["batch"] * w["bag"]
+    w["working_set"] = min(sum(w["rows"]), n) * w["dim"] * 4 * 2 + n * w["dim"] * 4 // max(w["bag"], 1)
+    if args.impl == "reference":
+        run_reference_arm(args, w)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()

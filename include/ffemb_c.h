@@ -1,0 +1,374 @@
+/* ffemb_c.h -- C-ABI of the B200-native DLRM embedding-bag path.
+ *
+ * Drop-in boundary for ONE hot path of TravisDai/DLRM-FlexFlow: the embedding
+ * operator (forward gather-and-pool, backward, SGD row update, table-wise
+ * placement).  Written in the idiom of the reference's python/flexflow_c.h:
+ * extern "C", opaque `struct { void *impl; }` handles, plain pointers and
+ * sizes, no C++ and no torch types, parseable by `gcc -E | cffi.cdef`.
+ *
+ * Two layers:
+ *
+ *   (K) kernel-level entry points -- stateless, device pointers in, device
+ *       pointers out, explicit stream.  These are what the reference's Legion
+ *       task bodies would call in place of their own kernel launches
+ *       (Embedding::forward_task / backward_task, SGDOptimizer::update_task,
+ *       UniformInitializer::init_task).  INTEGRATION.md shows the patch.
+ *
+ *   (M) model-level entry points -- the flexflow_c.h surface for this path
+ *       (config / model / tensor / op / parameter / optimizer / initializer
+ *       handles; add_embedding, compile, forward, zero_gradients, backward,
+ *       update, get/set_weights), each citing the flexflow_c.h declaration it
+ *       stands in for.  Names carry the prefix ffemb_ instead of flexflow_ so
+ *       both libraries can live in one process.
+ *
+ * Conventions (differences from the reference are deliberate):
+ *   - every call that can fail returns an int status (FFEMB_OK = 0); the
+ *     message is available from ffemb_last_error().  Nothing aborts.
+ *   - a model handle is not thread-safe; one host thread per GPU.
+ *   - no hidden device synchronisation: calls enqueue on the given stream (or
+ *     the model's stream) and return; ffemb_model_sync / the caller syncs.
+ *   - handles are owned by the caller (destroy them); data buffers passed in
+ *     are borrowed for the call; tables are owned by the library.
+ *   - all tables / outputs / gradients fp32, all indices int64.
+ *   - tables are row-major [num_entries][out_dim]; index streams are
+ *     flattened [bag][position]; bag order is summation order.
+ *   - There is no CPU fallback: without a CUDA device every compute call
+ *     returns FFEMB_ERR_CUDA.
+ */
+#ifndef FFEMB_C_H
+#define FFEMB_C_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "ffemb_const.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FFEMB_MAX_PARTS 16 /* sample-blocks (ranks) one matrix may be split over */
+
+/* ------------------------------------------------------------------------
+ * Library
+ * --------------------------------------------------------------------- */
+
+/* Message of the last failing call on this host thread ("" if none). */
+const char *ffemb_last_error(void);
+
+/* "major.minor.patch"; sm architecture the kernels were compiled for. */
+const char *ffemb_version(void);
+int ffemb_compiled_sm(void);
+
+/* Number of this library's own kernels launched so far by this process
+ * (all streams).  Used by bench.py for its gpu_launches figure. */
+int64_t ffemb_kernel_launch_count(void);
+
+/* ------------------------------------------------------------------------
+ * (K) Kernel-level entry points
+ * --------------------------------------------------------------------- */
+
+/* One table's share of a batched launch.
+ * Stands in for the three regions of Embedding::forward_task
+ * (src/ops/embedding.cu:226-263: input, output, kernel). */
+typedef struct ffemb_lookup_t {
+  float *weight;          /* device, [num_entries][out_dim], 16-byte aligned  */
+  const int64_t *indices; /* device, flattened [bag][position]               */
+  const int64_t *offsets; /* device, batch+1 CSR bag offsets; NULL = fixed   */
+  int64_t num_entries;    /* rows of the table                               */
+  int64_t num_indices;    /* indices in this batch (batch*bag_size if fixed) */
+  int64_t col;            /* offset (floats) of this table's block from the
+                             start of a row of the output / gradient matrix:
+                             its first column in a [batch][T*D] concat
+                             matrix; any float offset from base[0] when the
+                             tables' blocks are separate allocations that
+                             share one row stride                            */
+  int32_t bag_size;       /* indices per bag when offsets == NULL            */
+  int32_t reserved;       /* set to 0                                        */
+} ffemb_lookup_t;
+
+/* A sample-major fp32 matrix, optionally split into equal blocks of
+ * consecutive samples ("parts"), each with its own base pointer: part r holds
+ * samples [r*rows_per_part, (r+1)*rows_per_part).  With num_parts == 1 it is
+ * an ordinary [batch][ld] matrix.  With num_parts == world size and base[r]
+ * pointing into rank r's memory (peer mapping, ffemb_comm_*) it expresses the
+ * reference's table-wise -> sample-wise repartition done at Concat
+ * (src/ops/concat.cu:85-93) without a separate exchange step. */
+typedef struct ffemb_matrix_t {
+  float *base[FFEMB_MAX_PARTS];
+  int32_t num_parts;
+  int32_t rows_per_part;
+  int64_t ld; /* row stride in floats */
+} ffemb_matrix_t;
+
+/* Forward gather-and-pool over `num_tables` tables in one batched launch.
+ *   out[b, col_t + d] = sum_{j in bag b of table t} W_t[idx, d]   (+0 start,
+ *   bag order), times 1.0f/len for AGGR_MODE_AVG (CPU semantics).
+ * Replaces embed_forward<<<>>> (src/ops/embedding.cu:173-197, launch :254)
+ * and EmbeddingLookup_int64_t_float_float__avx2_fma
+ * (src/ops/embedding_avx2.cc:5-296).  `lookups` is a HOST array.
+ * An out-of-range index contributes nothing and sets *err_flag (device int,
+ * may be NULL) to FFEMB_ERR_INDEX_OUT_OF_RANGE. */
+int ffemb_embed_forward(const ffemb_lookup_t *lookups, int num_tables,
+                        int batch, int out_dim, enum AggrMode aggr,
+                        const ffemb_matrix_t *out, int *err_flag,
+                        void *stream);
+
+/* Scratch bytes ffemb_embed_backward_sgd needs for a batch with
+ * `total_indices` lookups over tables with `total_entries` rows in all. */
+size_t ffemb_embed_backward_workspace_bytes(int64_t total_indices,
+                                            int64_t total_entries,
+                                            int out_dim);
+
+/* Deterministic backward fused with the sparse SGD row update:
+ *   sort (table,row) keys, segment-reduce duplicate rows in original
+ *   (bag, position) order, W[row,:] = fmaf(-lr, gsum, W[row,:]) on touched
+ *   rows only.
+ * Replaces embed_backward<<<>>> (src/ops/embedding.cu:199-224, launch :318),
+ * the dense zero of the gradient (src/runtime/initializer_kernel.cu:232-262)
+ * and dense sgd_update<<<>>> (src/runtime/optimizer_kernel.cu:23-41,104-106)
+ * for weight_decay == 0 and momentum == 0, where the three are equivalent.
+ * `grad` is d(loss)/d(out) in the layout of ffemb_embed_forward's `out`.
+ * `workspace` is device memory of at least
+ * ffemb_embed_backward_workspace_bytes() bytes, 256-byte aligned. */
+int ffemb_embed_backward_sgd(const ffemb_lookup_t *lookups, int num_tables,
+                             int batch, int out_dim, enum AggrMode aggr,
+                             const ffemb_matrix_t *grad, float lr,
+                             void *workspace, size_t workspace_bytes,
+                             int *err_flag, void *stream);
+
+/* The two halves of ffemb_embed_backward_sgd, for callers that keep the
+ * reference's backward() / update() split: `backward_sort` leaves the sorted
+ * sparse gradient description in `workspace`; `sgd_update` consumes it.
+ * (Embedding::backward, src/ops/embedding.cu:329-355; SGDOptimizer::update,
+ * src/runtime/optimizer.cc:75-102.) */
+int ffemb_embed_backward_sort(const ffemb_lookup_t *lookups, int num_tables,
+                              int batch, int out_dim, void *workspace,
+                              size_t workspace_bytes, int *err_flag,
+                              void *stream);
+int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tables,
+                           int batch, int out_dim, enum AggrMode aggr,
+                           const ffemb_matrix_t *grad, float lr,
+                           void *workspace, size_t workspace_bytes,
+                           void *stream);
+
+/* W[i] = (max-min) * u_i + min, u_i in (0,1] from a counter-based generator
+ * keyed by (seed, i).  Stands in for UniformInitializer::init_task
+ * (src/runtime/initializer_kernel.cu:24-85) + scale_kernel
+ * (src/runtime/cuda_helper.cu:3-11); same distribution, reproducible stream. */
+int ffemb_uniform_init(float *weight, int64_t count, int seed, float min_val,
+                       float max_val, void *stream);
+
+/* ------------------------------------------------------------------------
+ * (M) Model-level entry points (flexflow_c.h surface for this path)
+ * --------------------------------------------------------------------- */
+
+#define FFEMB_NEW_OPAQUE_TYPE(T) typedef struct T { void *impl; } T
+
+FFEMB_NEW_OPAQUE_TYPE(ffemb_config_t);            /* flexflow_c.h:27 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_model_t);             /* :28 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_tensor_t);            /* :29 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_sgd_optimizer_t);     /* :30 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_initializer_t);       /* :32 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_zero_initializer_t);  /* :34 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_uniform_initializer_t); /* :35 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_op_t);                /* :37 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_parameter_t);         /* :38 */
+FFEMB_NEW_OPAQUE_TYPE(ffemb_strategy_t);          /* FFProtoBuf::Strategy */
+
+/* --- FFConfig (flexflow_c.h:49-79; flags of src/runtime/model.cc:1313-1381) */
+ffemb_config_t ffemb_config_create(void);
+void ffemb_config_destroy(ffemb_config_t handle);
+/* "-b" batch size (global batch: every embedding op sees the whole batch,
+ * reference strategy dims [1,1]); "-ll:gpu" workers per node; "--nodes". */
+int ffemb_config_set_batch_size(ffemb_config_t handle, int batch_size);
+int ffemb_config_get_batch_size(ffemb_config_t handle);
+int ffemb_config_set_workers_per_node(ffemb_config_t handle, int n);
+int ffemb_config_get_workers_per_node(ffemb_config_t handle);
+int ffemb_config_set_num_nodes(ffemb_config_t handle, int n);
+int ffemb_config_get_num_nodes(ffemb_config_t handle);
+/* This process's rank in [0, workers_per_node*num_nodes) and CUDA device.
+ * (The reference is one process for all GPUs under Legion; here it is one
+ * process per GPU.) */
+int ffemb_config_set_rank(ffemb_config_t handle, int rank, int cuda_device);
+int ffemb_config_get_rank(ffemb_config_t handle);
+/* "--import[-strategy] <file>" (src/mapper/mapper.cc:282-286). */
+int ffemb_config_import_strategy_file(ffemb_config_t handle, const char *path);
+
+/* --- FFModel (flexflow_c.h:86-135) */
+ffemb_model_t ffemb_model_create(ffemb_config_t config);
+void ffemb_model_destroy(ffemb_model_t handle);
+
+/* flexflow_tensor_create (flexflow_c.h:371-378): a model input.  On this path
+ * that is the sparse input of one table: dims = {batch, bag_size}, DT_INT64
+ * (examples/cpp/DLRM/dlrm.cc:100-108). */
+ffemb_tensor_t ffemb_tensor_create(ffemb_model_t model, int num_dims,
+                                   const int *dims, const char *name,
+                                   enum DataType data_type, bool create_grad);
+void ffemb_tensor_destroy(ffemb_tensor_t handle);
+int ffemb_tensor_get_num_dims(ffemb_tensor_t handle);
+int ffemb_tensor_get_dim(ffemb_tensor_t handle, int axis);
+int ffemb_tensor_get_data_type(ffemb_tensor_t handle);
+
+/* flexflow_model_add_embedding (flexflow_c.h:193-200; flexflow_c.cc:376-393;
+ * FFModel::embedding, src/ops/embedding.cu:19-33).  Same argument order and
+ * meaning, including the reference's spelling `num_entires`.  `shared_op`
+ * only shares the op name, not storage (src/runtime/model.cc:164-169).
+ * Returns the output tensor [batch, out_dim] DT_FLOAT; impl == NULL on error. */
+ffemb_tensor_t ffemb_model_add_embedding(ffemb_model_t handle,
+                                         const ffemb_tensor_t input,
+                                         int num_entires, int out_dim,
+                                         enum AggrMode aggr,
+                                         ffemb_op_t shared_op,
+                                         ffemb_initializer_t kernel_initializer);
+
+/* flexflow_model_set_sgd_optimizer (flexflow_c.h:338-341). */
+int ffemb_model_set_sgd_optimizer(ffemb_model_t handle,
+                                  ffemb_sgd_optimizer_t optimizer);
+
+/* flexflow_model_compile (flexflow_c.h:122-127): allocates the tables this
+ * rank owns under the placement, runs the initialisers, sizes the backward
+ * workspace.  Loss/metrics arguments of the reference do not exist on this
+ * path. */
+int ffemb_model_compile(ffemb_model_t handle);
+/* flexflow_model_init_layers (:98-100) -- EMBED_INIT_TASK is a no-op in the
+ * reference too (src/ops/embedding.cu:137-144). */
+int ffemb_model_init_layers(ffemb_model_t handle);
+/* flexflow_model_forward / zero_gradients / backward / update (:106-135).
+ * zero_gradients is a no-op: no dense gradient exists.  backward builds the
+ * sorted sparse gradient; update applies SGD to the touched rows. */
+int ffemb_model_forward(ffemb_model_t handle);
+int ffemb_model_zero_gradients(ffemb_model_t handle);
+int ffemb_model_backward(ffemb_model_t handle);
+int ffemb_model_update(ffemb_model_t handle);
+/* Blocks until the model's stream is idle, then reports (and clears) a
+ * pending out-of-range-index error. */
+int ffemb_model_sync(ffemb_model_t handle);
+/* Use `stream` (a cudaStream_t) for all model work; NULL = default stream. */
+int ffemb_model_set_stream(ffemb_model_t handle, void *stream);
+
+int ffemb_model_get_num_layers(ffemb_model_t handle);
+ffemb_op_t ffemb_model_get_layer_by_id(ffemb_model_t handle, int layer_id);
+
+/* --- Op (flexflow_c.h:720-743) */
+ffemb_parameter_t ffemb_op_get_parameter_by_id(ffemb_op_t handle, int id);
+ffemb_tensor_t ffemb_op_get_input_by_id(ffemb_op_t handle, int id);
+ffemb_tensor_t ffemb_op_get_output_by_id(ffemb_op_t handle, int id);
+/* "Embed_<N>x<D>_<guid>" (src/runtime/model.cc:157-171) */
+const char *ffemb_op_get_name(ffemb_op_t handle);
+/* Rank that owns this table under the compiled placement. */
+int ffemb_op_get_device(ffemb_op_t handle);
+
+/* --- Tensor data movement.  The reference moves data with dataloader tasks
+ * (examples/cpp/DLRM/dlrm.cu:19-56) and inline mappings
+ * (flexflow_tensor_inline_map, flexflow_c.h:395-430); here it is explicit. */
+/* Host -> device copy into an int64 input tensor (enqueued on the model
+ * stream; `data` should be pinned for the copy to be asynchronous). */
+int ffemb_tensor_set_int64(ffemb_tensor_t handle, ffemb_model_t model,
+                           const int64_t *data, int64_t count);
+/* Host -> device copy into a float tensor's gradient (d loss / d out). */
+int ffemb_tensor_set_grad_float(ffemb_tensor_t handle, ffemb_model_t model,
+                                const float *data, int64_t count);
+/* Device -> host copy of a float tensor (an embedding output). */
+int ffemb_tensor_get_float(ffemb_tensor_t handle, ffemb_model_t model,
+                           float *data, int64_t count);
+/* Borrow caller-owned device memory instead of the library's own buffer
+ * (torch tensors: data_ptr()).  `ld` is the row stride in elements; for an
+ * output tensor, attaching column blocks of one [batch][T*D] matrix yields
+ * the Concat layout directly.  grad = true attaches the gradient buffer. */
+int ffemb_tensor_attach_device_ptr(ffemb_tensor_t handle, void *device_ptr,
+                                   int64_t ld, bool grad);
+void *ffemb_tensor_get_device_ptr(ffemb_tensor_t handle, bool grad);
+int64_t ffemb_tensor_get_ld(ffemb_tensor_t handle, bool grad);
+
+/* --- Parameter (flexflow_c.h:447-459; src/runtime/model.cu:260-334).
+ * Layout is row-major [num_entries][out_dim] (what the reference's kernels
+ * index, src/ops/embedding.cu:189,221).  On a rank that does not own the
+ * table both calls fail with FFEMB_ERR_INVALID_ARGUMENT. */
+bool ffemb_parameter_set_weights_float(ffemb_parameter_t handle,
+                                       ffemb_model_t model, int num_dim,
+                                       const int *dims, const float *data);
+bool ffemb_parameter_get_weights_float(ffemb_parameter_t handle,
+                                       ffemb_model_t model, float *data);
+/* Device pointer of the table (NULL when not owned), for zero-copy wrapping. */
+float *ffemb_parameter_get_device_ptr(ffemb_parameter_t handle);
+int64_t ffemb_parameter_get_num_entries(ffemb_parameter_t handle);
+int ffemb_parameter_get_out_dim(ffemb_parameter_t handle);
+
+/* --- SGDOptimizer (flexflow_c.h:465-480; include/optimizer.h:36-54).
+ * The sparse fused update is exact only for momentum == 0 and
+ * weight_decay == 0 (DLRM: examples/cpp/DLRM/dlrm.cc:134); other settings
+ * make ffemb_model_update return FFEMB_ERR_UNSUPPORTED. */
+ffemb_sgd_optimizer_t ffemb_sgd_optimizer_create(ffemb_model_t model, double lr,
+                                                 double momentum, bool nesterov,
+                                                 double weight_decay);
+void ffemb_sgd_optimizer_destroy(ffemb_sgd_optimizer_t handle);
+void ffemb_sgd_optimizer_set_lr(ffemb_sgd_optimizer_t handle, double lr);
+
+/* --- Initializers (flexflow_c.h:526-545) */
+ffemb_uniform_initializer_t ffemb_uniform_initializer_create(int seed, float min,
+                                                             float max);
+void ffemb_uniform_initializer_destroy(ffemb_uniform_initializer_t handle);
+ffemb_zero_initializer_t ffemb_zero_initializer_create(void);
+void ffemb_zero_initializer_destroy(ffemb_zero_initializer_t handle);
+
+/* --- Placement: strategy files and the mapper hook.
+ * FFProtoBuf::Strategy wire format, src/runtime/strategy.proto:5-23;
+ * load/save, src/runtime/strategy.cc:96-172; FFMapper::slice_task,
+ * src/mapper/mapper.cc:33-97 (point -> devices[device_ids[i] % ndevices]). */
+ffemb_strategy_t ffemb_strategy_create(void);
+void ffemb_strategy_destroy(ffemb_strategy_t handle);
+int ffemb_strategy_load_file(ffemb_strategy_t handle, const char *path);
+int ffemb_strategy_save_file(ffemb_strategy_t handle, const char *path);
+int ffemb_strategy_parse(ffemb_strategy_t handle, const uint8_t *bytes, size_t n);
+/* Serialises into `bytes` (capacity `cap`); returns the size needed. */
+size_t ffemb_strategy_serialize(ffemb_strategy_t handle, uint8_t *bytes, size_t cap);
+int ffemb_strategy_num_ops(ffemb_strategy_t handle);
+const char *ffemb_strategy_op_name(ffemb_strategy_t handle, int i);
+int ffemb_strategy_op_device_type(ffemb_strategy_t handle, int i);
+int ffemb_strategy_op_num_dims(ffemb_strategy_t handle, int i);
+int ffemb_strategy_op_dim(ffemb_strategy_t handle, int i, int k);
+int ffemb_strategy_op_num_device_ids(ffemb_strategy_t handle, int i);
+int ffemb_strategy_op_device_id(ffemb_strategy_t handle, int i, int k);
+int ffemb_strategy_op_num_memory_types(ffemb_strategy_t handle, int i);
+int ffemb_strategy_op_memory_type(ffemb_strategy_t handle, int i, int k);
+int ffemb_strategy_add_op(ffemb_strategy_t handle, const char *name,
+                          int device_type, const int *dims, int num_dims,
+                          const int *device_ids, int num_device_ids,
+                          const int *memory_types, int num_memory_types);
+/* Index of the op called `name`, or -1 (the reference hashes the name,
+ * src/runtime/strategy.cc:23-26). */
+int ffemb_strategy_find(ffemb_strategy_t handle, const char *name);
+/* The generator of src/runtime/dlrm_strategy.cc:242-296: embedding<i> ->
+ * device i % (gpus_per_node*num_nodes); concat / linear / mse_loss entries as
+ * the reference writes them. */
+int ffemb_strategy_generate_dlrm(ffemb_strategy_t handle, int gpus_per_node,
+                                 int embs_per_node, int num_nodes);
+/* The generator of src/runtime/dlrm_strategy.py:26-46, which produced the
+ * reference's checked-in dlrm_strategy_<E>embs_<G>gpus.pb fixtures:
+ * embedding<i> -> dims [1,1], device i % num_gpu; linear, mse_loss, concat ->
+ * dims [1,num_gpu], devices 0..num_gpu-1.  Byte-identical output. */
+int ffemb_strategy_generate_dlrm_simple(ffemb_strategy_t handle, int num_gpu,
+                                        int num_emb);
+/* Mapper hook: device of table `table_index` (also looked up under the names
+ * "embedding<i>" and `op_name`), folded by `% num_devices` as slice_task
+ * does; round-robin table_index % num_devices when the strategy has no entry
+ * (or handle.impl == NULL). */
+int ffemb_strategy_device_for_table(ffemb_strategy_t handle, int table_index,
+                                    const char *op_name, int num_devices);
+/* Cost-aware placement (the reference cannot cost embeddings,
+ * src/ops/embedding.cu:357-364): greedy longest-processing-time assignment of
+ * tables to devices by lookups per step, subject to bytes_capacity per
+ * device.  Writes device ids into owner[num_tables].  */
+int ffemb_placement_balance(const int64_t *num_entries, const int64_t *lookups,
+                            int num_tables, int out_dim, int num_devices,
+                            int64_t bytes_capacity, int *owner);
+/* Model-level: use this strategy at compile (overrides the config's file). */
+int ffemb_model_set_strategy(ffemb_model_t model, ffemb_strategy_t strategy);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* FFEMB_C_H */
