@@ -2,23 +2,25 @@
 //
 // Replaces, for weight_decay == momentum == 0 (DLRM's optimiser,
 // examples/cpp/DLRM/dlrm.cc:134), three dense reference passes per step:
-//   zero of the [N][D] gradient    src/runtime/initializer_kernel.cu:232-262
+//   zero of the [N][D] gradient       src/runtime/initializer_kernel.cu:232-262
 //   atomicAdd scatter embed_backward  src/ops/embedding.cu:199-224
-//   dense sgd_update over N*D      src/runtime/optimizer_kernel.cu:23-41
+//   dense sgd_update over N*D         src/runtime/optimizer_kernel.cu:23-41
 // by work proportional to the lookups of the step:
 //   1. make_keys   key = table_row_base + row, val = table*B + bag
 //   2. stable LSD radix sort of (key, val) on the significant key bits
 //   3. reduce_l1   one sub-warp per chunk of 32 sorted positions: gradient
-//                  rows added in sorted (= original (bag, position)) order;
-//                  a run that starts and ends inside the chunk is applied at
-//                  once: W[row,:] = fmaf(-lr, gsum, W[row,:]); a run cut by a
-//                  chunk boundary leaves a partial sum
-//   4. reduce_l2   the chunk where such a run starts adds the partials in
-//                  chunk order and applies the update.
-// No atomics; the result depends only on the inputs (bitwise repeatable).
-// Rows whose lookups all fall in one chunk get the exact sequential sum of
-// the reference's CPU backward (src/ops/embedding.cc:54-72); longer runs are
-// summed chunk-wise (still a fixed order), within 1e-5 of it.
+//                  rows added in sorted (= original (bag, position)) order; a
+//                  run inside the chunk is applied at once,
+//                  W[row,:] = fmaf(-lr, gsum, W[row,:]); runs cut by chunk
+//                  boundaries are chained in shared memory inside the block;
+//                  only runs that leave the block reach memory as partials
+//   4. reduce_l2 / reduce_l3   the block in which such a run starts adds the
+//                  following blocks' partials in order (one sub-warp for
+//                  short chains, one block for long ones) and applies it.
+// No floating-point atomics; the result depends only on the inputs (bitwise
+// repeatable).  Rows whose lookups all fall in one chunk get the exact
+// sequential sum of the reference's CPU backward (src/ops/embedding.cc:54-72);
+// longer runs are summed piecewise in a fixed order, within 1e-5 of it.
 #include <cub/device/device_radix_sort.cuh>
 
 #include "ffemb_common.cuh"
@@ -27,7 +29,8 @@ namespace ffemb {
 
 constexpr int kChunk = 32;  // sorted positions per sub-warp in reduce_l1
 constexpr int kBwdThreads = 256;
-constexpr int kBU = 8;  // positions whose rows are in flight together
+constexpr int kBU = 8;            // positions whose rows are in flight together
+constexpr int kShortChain = 32;   // reduce_l2 sums chains up to this many partials itself
 
 struct KeyTable {  // make_keys view
   const int64_t *idx;
@@ -60,9 +63,12 @@ struct BwdParams {
   Matrix grad;
   const void *keys;
   const uint32_t *vals;
-  float *part0;  // [chunks][D] partial of the run that enters the chunk
-  float *part1;  // [chunks][D] partial of the run that leaves the chunk
-  int64_t n;
+  float *part0;      // [blocks][D] partial of the run that enters a level-1 block
+  float *part1;      // [blocks][D] partial of the run that leaves it
+  int *counters;     // [0] chains, [1] long chains
+  int *owners;       // blocks in which a leaving run starts
+  int2 *long_owners; // (first block, last block) of chains longer than kShortChain
+  int n;
   int T;
   int B;
   int D;
@@ -166,151 +172,326 @@ __device__ __forceinline__ float4 sgd_row(float lr, const float4 &g, const float
                      fmaf(-lr, g.w, w.w));
 }
 
+template <typename P>
+__device__ __forceinline__ P *shfl_ptr(unsigned mask, P *ptr, int src, int width) {
+  return (P *)__shfl_sync(mask, (unsigned long long)ptr, src, width);
+}
+
+// Largest t with row_base[t] <= key (T <= 64: six halvings).
+template <typename KeyT>
+__device__ __forceinline__ int table_of(const BwdParams &p, KeyT key) {
+  int lo = 0, hi = p.T;
+#pragma unroll
+  for (int it = 0; it < 6; ++it) {
+    const int mid = (lo + hi) >> 1;
+    if (hi - lo > 1) {
+      if (p.t[mid].row_base <= (int64_t)key)
+        lo = mid;
+      else
+        hi = mid;
+    }
+  }
+  return lo;
+}
+
 // ---------------------------------------------------------------------------
-// 3. level-1 segmented reduce + SGD on complete runs.
+// 3. level-1 segmented reduce + SGD.
+//
+// Per chunk of 32 sorted positions, each lane of the sub-warp first works out
+// its own positions' bookkeeping (key, neighbours' keys, table, gradient-row
+// and table-row addresses, head/tail of a run); ballots turn head/tail/valid
+// into bit masks.  The walk itself then only shuffles the two addresses of a
+// position round the sub-warp: 8 gradient rows and the table rows of the runs
+// ending among them are in flight together and are consumed strictly in
+// order.  Runs cut by a chunk boundary leave a partial in shared memory;
+// after one barrier the sub-warp in whose chunk such a run starts adds the
+// following chunks' partials in order, so only runs that leave the BLOCK
+// (256/G chunks) reach global memory as partials.
 // ---------------------------------------------------------------------------
+constexpr int kHasLead = 1;   // first run of the chunk started before the chunk
+constexpr int kLeadCont = 2;  // ... and also continues past the end of the chunk
+constexpr int kHasTrail = 4;  // last run started in the chunk and continues past it
+
 template <typename KeyT, int G, bool VEC>
 __global__ void __launch_bounds__(kBwdThreads, 2)
 reduce_l1_kernel(const __grid_constant__ BwdParams p) {
   constexpr int U = kBU;
+  constexpr int S = kBwdThreads / G;  // chunks (sub-warps) per block
+  constexpr int KPL = kChunk / G;     // positions per lane
   constexpr KeyT kInv = KeyTraits<KeyT>::kInvalid;
+  static_assert(G >= 4 && G <= 32, "sub-warp of 4..32 lanes");
+  __shared__ float4 s_lead[S][G];
+  __shared__ float4 s_trail[S][G];
+  __shared__ int s_flags[S];
   const KeyT *__restrict__ keys = (const KeyT *)p.keys;
-  const int64_t sub = (int64_t)blockIdx.x * (kBwdThreads / G) + threadIdx.x / G;
-  const int64_t i0 = sub * kChunk;
-  if (i0 >= p.n) return;
-  const int64_t i1 = i0 + kChunk < p.n ? i0 + kChunk : p.n;
+  const int s = threadIdx.x / G, gl = threadIdx.x % G;
+  const int subshift = (threadIdx.x & 31) / G * G;
+  const unsigned gmask = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+  const unsigned submask = gmask << subshift;
+  const int n = p.n;
+  const int i0 = (blockIdx.x * S + s) * kChunk;
+  const int cnt = n - i0 < kChunk ? n - i0 : kChunk;  // positions in this chunk (<= 0: none)
   const int D = p.D;
-  Cols<VEC> cols{(int)(threadIdx.x % G), 0, D};
 
+  // ---- bookkeeping, one position per lane and register --------------------
+  const float *gptr[KPL];
+  float *wptr[KPL];
+  float glen[KPL];
+  unsigned headbits = 0, tailbits = 0, validbits = 0;
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const int q = j * G + gl, pos = i0 + q;
+    KeyT k = kInv, kp = kInv, kn = kInv;
+    uint32_t v = 0;
+    if (q < cnt) {
+      k = keys[pos];
+      v = p.vals[pos];
+      if (pos > 0) kp = keys[pos - 1];
+      if (pos + 1 < n) kn = keys[pos + 1];
+    }
+    const bool valid = k != kInv;
+    const bool head = valid && (pos == 0 || kp != k);
+    const bool tail = valid && kn != k;
+    gptr[j] = nullptr;
+    wptr[j] = nullptr;
+    glen[j] = 1.f;
+    if (valid) {
+      const int t = table_of(p, k);
+      const BwdTable &tb = p.t[t];
+      const int b = (int)(v - (uint32_t)t * (uint32_t)p.B);
+      gptr[j] = matrix_row(p.grad, b) + tb.col;
+      wptr[j] = tb.W + ((int64_t)k - tb.row_base) * D;
+      if (p.avg) glen[j] = tb.off ? (float)(int)(tb.off[b + 1] - tb.off[b]) : (float)tb.L;
+    }
+    validbits |= ((__ballot_sync(0xffffffffu, valid) >> subshift) & gmask) << (j * G);
+    headbits |= ((__ballot_sync(0xffffffffu, head) >> subshift) & gmask) << (j * G);
+    tailbits |= ((__ballot_sync(0xffffffffu, tail) >> subshift) & gmask) << (j * G);
+  }
+
+  Cols<VEC> cols{gl, 0, D};
   for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
     cols.d0 = d0;
-    KeyT kprev = i0 > 0 ? keys[i0 - 1] : kInv;
-    bool head_in_chunk = (i0 == 0) || (kprev != keys[i0]);
-    const bool first_is_head = head_in_chunk;
-    int t = 0;
+    int flags = 0;
+    bool head_in_chunk = false;
+    float *wlast = nullptr;  // table row of the run that leaves the chunk
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int64_t base = i0; base < i1; base += U) {
-      KeyT k[U + 1];
-      uint32_t gr[U];
 #pragma unroll
-      for (int u = 0; u <= U; ++u) k[u] = (base + u < p.n) ? keys[base + u] : kInv;
+    for (int base = 0; base < kChunk; base += U) {
+      if (base < cnt) {
+        float4 gv[U], wv[U];
+        float *wp[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) gr[u] = (base + u < i1) ? p.vals[base + u] : 0u;
-      float4 gv[U], wv[U];
-      float *wrow[U];
+        for (int u = 0; u < U; ++u) {
+          const int q = base + u;
+          const float *gp = shfl_ptr(submask, gptr[q / G], q % G, G);
+          wp[u] = shfl_ptr(submask, wptr[q / G], q % G, G);
+          gv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          wv[u] = gv[u];
+          if ((validbits >> q) & 1u) {
+            gv[u] = cols.ld_nc(gp);
+            if ((tailbits >> q) & 1u) wv[u] = cols.ld(wp[u]);
+          }
+        }
+        if (p.avg) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        gv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        wv[u] = gv[u];
-        wrow[u] = nullptr;
-        if (base + u < i1 && k[u] != kInv) {
-          while (t + 1 < p.T && (int64_t)k[u] >= p.t[t + 1].row_base) ++t;
-          const BwdTable &tb = p.t[t];
-          const int b = (int)(gr[u] - (uint32_t)t * (uint32_t)p.B);
-          gv[u] = cols.ld_nc(matrix_row(p.grad, b) + tb.col);
-          if (p.avg) {
-            const float len = tb.off ? (float)(int)(tb.off[b + 1] - tb.off[b]) : (float)tb.L;
+          for (int u = 0; u < U; ++u) {
+            const int q = base + u;
+            const float len = __shfl_sync(submask, glen[q / G], q % G, G);
             gv[u].x /= len;
             gv[u].y /= len;
             gv[u].z /= len;
             gv[u].w /= len;
           }
-          if (k[u] != k[u + 1]) {
-            wrow[u] = tb.W + ((int64_t)k[u] - tb.row_base) * D;
-            wv[u] = cols.ld(wrow[u]);
-          }
         }
-      }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (base + u < i1 && k[u] != kInv) {
-          const bool is_head =
-              (base + u == i0) ? first_is_head : (k[u] != (u == 0 ? kprev : k[u - 1]));
-          if (is_head) {
-            acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            head_in_chunk = true;
-          }
-          add4(acc, gv[u]);
-          if (k[u] != k[u + 1]) {  // true end of the run
-            if (head_in_chunk)
-              cols.st(wrow[u], sgd_row(p.lr, acc, wv[u]));
-            else
-              cols.st(p.part0 + sub * D, acc);
-          } else if (base + u == i1 - 1) {  // run continues in the next chunk
-            cols.st((head_in_chunk ? p.part1 : p.part0) + sub * D, acc);
+        for (int u = 0; u < U; ++u) {
+          const int q = base + u;
+          if ((validbits >> q) & 1u) {
+            if ((headbits >> q) & 1u) {
+              acc = make_float4(0.f, 0.f, 0.f, 0.f);
+              head_in_chunk = true;
+            }
+            add4(acc, gv[u]);
+            if ((tailbits >> q) & 1u) {  // true end of the run
+              if (head_in_chunk) {
+                cols.st(wp[u], sgd_row(p.lr, acc, wv[u]));
+              } else {
+                s_lead[s][gl] = acc;
+                flags |= kHasLead;
+              }
+            } else if (q == cnt - 1) {  // run continues in the next chunk
+              if (head_in_chunk) {
+                s_trail[s][gl] = acc;
+                flags |= kHasTrail;
+              } else {
+                s_lead[s][gl] = acc;
+                flags |= kHasLead | kLeadCont;
+              }
+              wlast = wp[u];
+            }
           }
         }
       }
-      kprev = k[U - 1];
+    }
+    if (gl == 0) s_flags[s] = flags;
+    __syncthreads();
+    // Chains inside the block.  The run entering the block (chunk 0's lead)
+    // and every run that starts in a chunk and leaves it are each summed by
+    // one sub-warp, following chunks in order.
+    if ((flags & kHasLead) && s == 0) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      add4(a, s_lead[0][gl]);
+      bool cont = flags & kLeadCont;
+      for (int s2 = 1; cont && s2 < S; ++s2) {
+        add4(a, s_lead[s2][gl]);
+        cont = s_flags[s2] & kLeadCont;
+      }
+      cols.st(p.part0 + (int64_t)blockIdx.x * D, a);
+    }
+    if (flags & kHasTrail) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      add4(a, s_trail[s][gl]);
+      bool cont = true;
+      for (int s2 = s + 1; cont && s2 < S; ++s2) {
+        add4(a, s_lead[s2][gl]);
+        cont = s_flags[s2] & kLeadCont;
+      }
+      if (cont) {  // leaves the block: level 2 finishes it
+        cols.st(p.part1 + (int64_t)blockIdx.x * D, a);
+        if (gl == 0 && d0 == 0) p.owners[atomicAdd(&p.counters[0], 1)] = blockIdx.x;
+      } else {
+        cols.st(wlast, sgd_row(p.lr, a, cols.ld(wlast)));
+      }
+    }
+    if (!VEC) __syncthreads();  // shared partials are reused by the next column tile
+  }
+}
+
+// ---------------------------------------------------------------------------
+// 4. level-2: runs that cross block boundaries ("chains").  One sub-warp per
+// chain: finds the last block the run reaches (keys are sorted: gallop, then
+// bisect), adds the entering partials of the following blocks in order and
+// applies the update.  Chains longer than kShortChain go to reduce_l3.
+// ---------------------------------------------------------------------------
+template <typename KeyT, int G, bool VEC>
+__global__ void __launch_bounds__(kBwdThreads)
+reduce_l2_kernel(const __grid_constant__ BwdParams p) {
+  constexpr int S = kBwdThreads / G;
+  constexpr int kSpan = S * kChunk;
+  const KeyT *__restrict__ keys = (const KeyT *)p.keys;
+  const int n = p.n, D = p.D;
+  const int nspans = (n + kSpan - 1) / kSpan;
+  const int count = p.counters[0];
+  Cols<VEC> cols{(int)(threadIdx.x % G), 0, D};
+  for (int o = blockIdx.x * S + threadIdx.x / G; o < count; o += gridDim.x * S) {
+    const int c = p.owners[o];
+    const KeyT key = keys[(c + 1) * kSpan - 1];
+    // last span whose first key is still `key` (span c+1 is, by construction)
+    int lo = c + 1, step = 1;
+    while (lo + step < nspans && keys[(int64_t)(lo + step) * kSpan] == key) {
+      lo += step;
+      step *= 2;
+    }
+    int hi = lo + step < nspans ? lo + step : nspans;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (keys[(int64_t)mid * kSpan] == key)
+        lo = mid;
+      else
+        hi = mid;
+    }
+    const int last = lo;
+    if (last - c > kShortChain) {
+      if (threadIdx.x % G == 0) p.long_owners[atomicAdd(&p.counters[1], 1)] = make_int2(c, last);
+      continue;
+    }
+    const int t = table_of(p, key);
+    float *wrow = p.t[t].W + ((int64_t)key - p.t[t].row_base) * D;
+    for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
+      cols.d0 = d0;
+      const float4 w = cols.ld(wrow);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      add4(acc, cols.ld(p.part1 + (int64_t)c * D));
+      for (int b = c + 1; b <= last; b += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (b + j <= last) v[j] = cols.ld(p.part0 + (int64_t)(b + j) * D);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (b + j <= last) add4(acc, v[j]);
+      }
+      cols.st(wrow, sgd_row(p.lr, acc, w));
     }
   }
 }
 
 // ---------------------------------------------------------------------------
-// 4. level-2: the chunk in which a boundary-crossing run starts owns it.
+// 5. level-3: long chains, one block each.  The sub-warps sum contiguous
+// slices of the chain, then sub-warp 0 adds the slices in order.
 // ---------------------------------------------------------------------------
 template <typename KeyT, int G, bool VEC>
 __global__ void __launch_bounds__(kBwdThreads)
-reduce_l2_kernel(const __grid_constant__ BwdParams p) {
-  constexpr KeyT kInv = KeyTraits<KeyT>::kInvalid;
+reduce_l3_kernel(const __grid_constant__ BwdParams p) {
+  constexpr int S = kBwdThreads / G;
+  constexpr int kSpan = S * kChunk;
+  __shared__ float4 s_part[S][G];
   const KeyT *__restrict__ keys = (const KeyT *)p.keys;
-  const int64_t c = (int64_t)blockIdx.x * (kBwdThreads / G) + threadIdx.x / G;
-  const int64_t i0 = c * kChunk;
-  const int64_t i1 = i0 + kChunk;  // first position of the next chunk
-  if (i1 >= p.n) return;           // no next chunk: nothing can leave this one
-  const KeyT key = keys[i1 - 1];
-  if (key == kInv || keys[i1] != key) return;  // last run ends here
-  // the leaving run starts in this chunk?
-  if (!(keys[i0] != key || i0 == 0 || keys[i0 - 1] != key)) return;
-  int t = 0;
-  while (t + 1 < p.T && (int64_t)key >= p.t[t + 1].row_base) ++t;
   const int D = p.D;
-  float *wrow = p.t[t].W + ((int64_t)key - p.t[t].row_base) * D;
-  Cols<VEC> cols{(int)(threadIdx.x % G), 0, D};
-  for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
-    cols.d0 = d0;
-    const float4 w = cols.ld(wrow);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    add4(acc, cols.ld(p.part1 + c * D));
-    int64_t cc = c + 1;
-    bool more = true;
-    while (more) {
-      // up to 4 following chunks at a time; chunk cc+j takes part while the
-      // run reaches it, i.e. chunks cc..cc+j-1 are wholly inside the run.
-      float4 v[4];
-      bool in[4], whole[4];
+  const int s = threadIdx.x / G, gl = threadIdx.x % G;
+  const int count = p.counters[1];
+  Cols<VEC> cols{gl, 0, D};
+  for (int o = blockIdx.x; o < count; o += gridDim.x) {
+    const int2 cl = p.long_owners[o];
+    const int c = cl.x, len = cl.y - cl.x;  // partials part0[c+1 .. c+len]
+    const int per = (len + S - 1) / S;
+    const int b0 = c + 1 + s * per;
+    const int b1 = b0 + per < c + 1 + len ? b0 + per : c + 1 + len;
+    for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
+      cols.d0 = d0;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int b = b0; b < b1; b += 8) {
+        float4 v[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int64_t s = (cc + j) * kChunk;  // first position of chunk cc+j
-        const int64_t e = s + kChunk;
-        in[j] = s < p.n && keys[s] == key;
-        whole[j] = in[j] && e < p.n && keys[e - 1] == key && keys[e] == key;
-        v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (in[j]) v[j] = cols.ld(p.part0 + (cc + j) * D);
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (more) {
-          if (in[j]) add4(acc, v[j]);
-          more = whole[j];
+        for (int j = 0; j < 8; ++j) {
+          v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (b + j < b1) v[j] = cols.ld(p.part0 + (int64_t)(b + j) * D);
         }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (b + j < b1) add4(acc, v[j]);
       }
-      cc += 4;
+      s_part[s][gl] = acc;
+      __syncthreads();
+      if (s == 0) {
+        const KeyT key = keys[(c + 1) * kSpan - 1];
+        const int t = table_of(p, key);
+        float *wrow = p.t[t].W + ((int64_t)key - p.t[t].row_base) * D;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        add4(a, cols.ld(p.part1 + (int64_t)c * D));
+        for (int s2 = 0; s2 < S; ++s2) add4(a, s_part[s2][gl]);
+        cols.st(wrow, sgd_row(p.lr, a, cols.ld(wrow)));
+      }
+      __syncthreads();
     }
-    cols.st(wrow, sgd_row(p.lr, acc, w));
   }
 }
 
 template <typename KeyT, int G, bool VEC>
 static void launch_reduce(const BwdParams &p, cudaStream_t s) {
-  const int64_t chunks = (p.n + kChunk - 1) / kChunk;
-  const int per_block = kBwdThreads / G;
-  const unsigned grid = (unsigned)((chunks + per_block - 1) / per_block);
-  reduce_l1_kernel<KeyT, G, VEC><<<grid, kBwdThreads, 0, s>>>(p);
+  constexpr int per_block = kBwdThreads / G;
+  const int64_t chunks = ((int64_t)p.n + kChunk - 1) / kChunk;
+  const int64_t blocks = (chunks + per_block - 1) / per_block;
+  reduce_l1_kernel<KeyT, G, VEC><<<(unsigned)blocks, kBwdThreads, 0, s>>>(p);
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  if (chunks > 1) {
-    reduce_l2_kernel<KeyT, G, VEC><<<grid, kBwdThreads, 0, s>>>(p);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (blocks > 1) {
+    // grids sized to the machine (148 SMs); both kernels stride over their lists
+    const int64_t want = (blocks + per_block - 1) / per_block;
+    reduce_l2_kernel<KeyT, G, VEC><<<(unsigned)(want < 148 * 4 ? want : 148 * 4), kBwdThreads, 0, s>>>(p);
+    reduce_l3_kernel<KeyT, G, VEC><<<(unsigned)(blocks < 148 * 2 ? blocks : 148 * 2), kBwdThreads, 0, s>>>(p);
+    g_launches.fetch_add(2, std::memory_order_relaxed);
   }
 }
 
@@ -318,12 +499,11 @@ template <typename KeyT>
 static void launch_reduce_g(const BwdParams &p, bool vec, cudaStream_t s) {
   if (!vec) return launch_reduce<KeyT, 32, false>(p, s);
   switch (p.D / 4) {
-    case 1: return launch_reduce<KeyT, 1, true>(p, s);
-    case 2: return launch_reduce<KeyT, 2, true>(p, s);
     case 4: return launch_reduce<KeyT, 4, true>(p, s);
     case 8: return launch_reduce<KeyT, 8, true>(p, s);
     case 16: return launch_reduce<KeyT, 16, true>(p, s);
-    default: return launch_reduce<KeyT, 32, true>(p, s);
+    case 32: return launch_reduce<KeyT, 32, true>(p, s);
+    default: return launch_reduce<KeyT, 32, false>(p, s);  // D = 4, 8: scalar columns
   }
 }
 
@@ -337,6 +517,8 @@ struct Workspace {
   void *sort_tmp;
   size_t sort_tmp_bytes;
   float *part0, *part1;
+  int *counters, *owners;
+  int2 *long_owners;
   size_t total;
 };
 
@@ -363,7 +545,8 @@ static Workspace carve(void *base, int64_t n, int64_t total_entries, int D) {
   Workspace w;
   const bool wide = wide_keys(total_entries);
   w.key_bytes = wide ? 8 : 4;
-  const int64_t chunks = (n + kChunk - 1) / kChunk;
+  // one partial pair per level-1 block; the smallest block span is 256 positions
+  const int64_t blocks = (n + 255) / 256 + 1;
   char *p = (char *)base;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -377,8 +560,11 @@ static Workspace carve(void *base, int64_t n, int64_t total_entries, int D) {
   w.vals_b = (uint32_t *)take(n * 4);
   w.sort_tmp_bytes = sort_tmp_bytes(n, wide);
   w.sort_tmp = take(w.sort_tmp_bytes);
-  w.part0 = (float *)take((size_t)chunks * D * 4);
-  w.part1 = (float *)take((size_t)chunks * D * 4);
+  w.part0 = (float *)take((size_t)blocks * D * 4);
+  w.part1 = (float *)take((size_t)blocks * D * 4);
+  w.counters = (int *)take(256);
+  w.owners = (int *)take((size_t)blocks * sizeof(int));
+  w.long_owners = (int2 *)take((size_t)blocks * sizeof(int2));
   w.total = off;
   return w;
 }
@@ -471,12 +657,16 @@ static int update_group(const ffemb_lookup_t *lookups, int T, int batch, int out
   bp.vals = w.vals_b;
   bp.part0 = w.part0;
   bp.part1 = w.part1;
-  bp.n = g.n;
+  bp.counters = w.counters;
+  bp.owners = w.owners;
+  bp.long_owners = w.long_owners;
+  bp.n = (int)g.n;
   bp.T = T;
   bp.B = batch;
   bp.D = out_dim;
   bp.avg = avg;
   bp.lr = lr;
+  FFEMB_CUDA_OK(cudaMemsetAsync(w.counters, 0, 2 * sizeof(int), s));
   if (wide_keys(g.total_entries))
     launch_reduce_g<uint64_t>(bp, vec, s);
   else
@@ -508,6 +698,8 @@ static int backward_impl(int phases, const ffemb_lookup_t *lookups, int num_tabl
   for (int t0 = 0; t0 < num_tables; t0 += kMaxTables) {
     const int T = num_tables - t0 < kMaxTables ? num_tables - t0 : kMaxTables;
     const Group g = group_of(lookups + t0, T);
+    if (g.n >= 0x7FFFFF00ll)
+      return fail(FFEMB_ERR_UNSUPPORTED, std::string(who) + ": more than 2^31 lookups in one launch group");
     Workspace w = carve((char *)workspace + off, g.n, g.total_entries, out_dim);
     if (off + w.total > workspace_bytes)
       return fail(FFEMB_ERR_WORKSPACE_TOO_SMALL,
@@ -533,10 +725,10 @@ using namespace ffemb;
 extern "C" size_t ffemb_embed_backward_workspace_bytes(int64_t total_indices,
                                                        int64_t total_entries, int out_dim) {
   if (total_indices < 0 || total_entries < 0 || out_dim <= 0) return 0;
-  // One group's layout for the whole problem, plus per-group alignment slack
-  // for callers with more than kMaxTables tables.
+  // One group's layout for the whole problem, plus per-group slack for
+  // callers with more than kMaxTables tables.
   Workspace w = carve(nullptr, total_indices, total_entries, out_dim);
-  return w.total + 16 * 256 * 8;
+  return w.total + (1u << 20);
 }
 
 extern "C" int ffemb_embed_backward_sgd(const ffemb_lookup_t *lookups, int num_tables, int batch,
