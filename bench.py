@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-row-cap", type=int, default=2_000_000)
     ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N>1: fused peer-memory exchange inside the kernels, or NCCL all-to-all")
+    ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balance"])
     return ap.parse_args()
 
 
@@ -222,7 +225,7 @@ def run_ours(args, w):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     if world > 1:
-        raise SystemExit("multi-GPU bench not wired yet")
+        return run_sharded(args, w, rank, world, local_rank)
 
     D, B, L, aggr = w["dim"], w["batch"], w["bag"], w["aggr"]
     rows = w["rows"]
@@ -380,6 +383,129 @@ def run_ours(args, w):
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         print(json.dumps(line), flush=True)
+
+
+def run_sharded(args, w, rank, world, local_rank):
+    """N > 1: tables sharded table-wise, one process per GPU, both exchanges
+    inside the step.  Time = max over ranks of the device time of K steps."""
+    import torch
+    import torch.distributed as dist
+    from dlrm_flexflow_b200 import kernels, workloads
+    from dlrm_flexflow_b200.sharded import ShardPlan, ShardedEmbeddingBags
+
+    D, B, L, aggr, rows = w["dim"], w["batch"], w["bag"], w["aggr"], w["rows"]
+    T = len(rows)
+    owners = None
+    if args.placement == "balance":
+        import dlrm_flexflow_b200 as ff
+        owners = ff.balance_placement(rows, [B * L] * T, D, world, 150 << 30)
+    plan = ShardPlan(rows, D, B, world, owners=owners)
+    sh = ShardedEmbeddingBags(plan, rank, L, aggr, args.lr, exchange=args.exchange)
+    mine = plan.tables_of(rank)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(4321 + rank)
+    pool = [[workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen) for t in mine]
+            for _ in range(args.pool)]
+    sh.grad.normal_(generator=gen)
+
+    def step(p, ev=None):
+        if ev:
+            ev[0].record()
+        sh.forward(pool[p])
+        if ev:
+            ev[1].record()
+        sh.backward_update(pool[p])
+        if ev:
+            ev[2].record()
+
+    for i in range(max(args.warmup, 3)):
+        step(i % args.pool)
+    sh.check_errors()
+    K = args.steps
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = kernels.kernel_launch_count()
+    dist.barrier()
+    torch.cuda.synchronize()
+    for i in range(K):
+        step((args.warmup + i) % args.pool, evs[i])
+    torch.cuda.synchronize()
+    dist.barrier()
+    launches = kernels.kernel_launch_count() - launches0
+    clocks = sampler.stop()
+    sh.check_errors()
+    t = torch.tensor([evs[0][0].elapsed_time(evs[-1][2]),
+                      sum(e[0].elapsed_time(e[1]) for e in evs), sum(e[1].elapsed_time(e[2]) for e in evs)],
+                     device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, fwd_ms, bwd_ms = (t / K).tolist()
+    uniq = torch.tensor([sum(int(torch.unique(x).numel()) for x in pool[(args.warmup + i) % args.pool])
+                         for i in range(min(K, args.pool))], device="cuda", dtype=torch.float64).mean().reshape(1)
+    my_u = float(uniq.item())
+    dist.all_reduce(uniq)
+    U = float(uniq.item())
+    peak, peak_src = measured_peaks()
+    n_lookups = T * B * L
+    step_bytes = n_lookups * D * 4 + 2 * U * D * 4
+    my_bytes = len(mine) * B * L * D * 4 + 2 * my_u * D * 4
+    xbytes = plan.exchange_bytes_per_rank(0)
+    line = {
+        "metric": METRIC, "value": B / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": args.warmup, "ms_per_step": total_ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, w, world),
+        "roofline": {"bound": "hbm", "kernel": "whole step on rank 0 (forward + sort + update + both exchanges)",
+                     "achieved": my_bytes / total_ms / 1e6, "peak": peak, "unit": "GB/s",
+                     "frac": my_bytes / total_ms / 1e6 / peak, "peak_source": peak_src, "traffic": None},
+        "step_roofline": {"algorithmic_bytes": step_bytes, "unique_rows": U, "lookups": n_lookups,
+                          "gbs_all_gpus": step_bytes / total_ms / 1e6,
+                          "frac_of_measured_peak_x_n": step_bytes / total_ms / 1e6 / (peak * world)},
+        "phases": {"forward_and_exchange": {"ms": fwd_ms}, "exchange_sort_update": {"ms": bwd_ms}},
+        "exchange": {"mode": args.exchange, "bytes_per_gpu_per_direction": xbytes,
+                     "fwd_lower_bound_bus_gbs": xbytes / fwd_ms / 1e6, "nvlink_peak_gbs": 900.0,
+                     "tables_per_rank": [len(plan.tables_of(r)) for r in range(world)],
+                     "imbalance_bound": plan.imbalance_bound()},
+        "clocks": clocks, "gpu_launches": int(launches),
+    }
+    line["config"]["placement"] = args.placement
+    if not args.no_e2e:
+        Bs = plan.Bs
+        idx_host = [x.cpu().pin_memory() for x in pool[0]]
+        idx_dev = [torch.empty_like(x) for x in pool[0]]
+        grad_host = torch.empty((Bs, T * D), pin_memory=True)
+        grad_host.copy_(sh.grad)
+        out_host = torch.empty((Bs, T * D), pin_memory=True)
+
+        def e2e_step():
+            for d, h in zip(idx_dev, idx_host):
+                d.copy_(h, non_blocking=True)
+            out = sh.forward(idx_dev)
+            out_host.copy_(out, non_blocking=True)
+            sh.grad.copy_(grad_host, non_blocking=True)
+            sh.backward_update(idx_dev)
+            torch.cuda.synchronize()
+
+        for _ in range(2):
+            e2e_step()
+        dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(args.e2e_steps):
+            e2e_step()
+        e.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([s.elapsed_time(e) / args.e2e_steps], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+        line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                       "h2d_bytes_per_step": sum(x.numel() for x in idx_host) * 8 + grad_host.numel() * 4,
+                       "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
+                       "note": "bytes are per rank; every rank copies its own slice"}
+    sh.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
 
 
 def main():

@@ -66,6 +66,11 @@ SIGNATURES = {
     "ffemb_embed_backward_sort": (_i, [_LP, _i, _i, _i, _vp, _sz, _vp, _vp]),
     "ffemb_embed_sgd_update": (_i, [_LP, _i, _i, _i, _i, _MP, _f, _vp, _sz, _vp]),
     "ffemb_uniform_init": (_i, [_vp, _i64, _i, _f, _f, _vp]),
+    "ffemb_device_malloc": (_i, [C.POINTER(C.c_void_p), _sz]),
+    "ffemb_device_free": (_i, [_vp]),
+    "ffemb_ipc_get_handle": (_i, [_vp, _vp]),
+    "ffemb_ipc_open_handle": (_i, [_vp, C.POINTER(C.c_void_p)]),
+    "ffemb_ipc_close_handle": (_i, [_vp]),
     # config
     "ffemb_config_create": (_H, []),
     "ffemb_config_destroy": (None, [_H]),

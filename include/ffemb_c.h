@@ -160,6 +160,22 @@ int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tables,
 int ffemb_uniform_init(float *weight, int64_t count, int seed, float min_val,
                        float max_val, void *stream);
 
+/* Peer-memory plumbing of the table-wise sharded path (one process per GPU).
+ * Stands in for what Legion DMA does for the reference: embedding outputs and
+ * their gradients cross GPUs through zero-copy host memory
+ * (src/ops/embedding.cu:280-284,343-347; src/ops/concat.cu:85-93).  A rank
+ * allocates its [batch/N][T*D] output and gradient matrices with
+ * ffemb_device_malloc (plain cudaMalloc: IPC-exportable), publishes the
+ * handles, opens its peers', and passes the mapped pointers as the parts of
+ * an ffemb_matrix_t: the forward kernel then stores pooled rows straight into
+ * the consuming rank's matrix over NVLink and the update kernel loads
+ * gradient rows straight from the producing rank's. */
+int ffemb_device_malloc(void **ptr, size_t bytes);
+int ffemb_device_free(void *ptr);
+int ffemb_ipc_get_handle(void *device_ptr, uint8_t handle[64]);
+int ffemb_ipc_open_handle(const uint8_t handle[64], void **device_ptr);
+int ffemb_ipc_close_handle(void *device_ptr);
+
 /* ------------------------------------------------------------------------
  * (M) Model-level entry points (flexflow_c.h surface for this path)
  * --------------------------------------------------------------------- */
