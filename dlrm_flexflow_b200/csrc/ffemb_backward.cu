@@ -758,3 +758,88 @@ extern "C" int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tab
   return backward_impl(kUpdate, lookups, num_tables, batch, out_dim, aggr == AGGR_MODE_AVG, grad,
                        lr, workspace, workspace_bytes, nullptr, stream);
 }
+
+// ---------------------------------------------------------------------------
+// ffemb_embed_backward_sgd_static -- the same backward + sparse SGD, for
+// callers that may not allocate device memory.
+//
+// Who that is: code running where cudaMalloc is forbidden or unsafe -- a
+// plugin called from inside a framework that owns the whole memory pool and
+// hands out no scratch, a real-time / serving loop that must not hit the
+// allocator's device-wide lock, a caller between other libraries' captures.
+// They cannot provide the workspace ffemb_embed_backward_sgd asks for, so
+// this variant brings its own: a fixed array that is part of the library
+// image.  Every GPU on which the library is loaded holds those
+// FFEMB_STATIC_SCRATCH_BYTES (8 MiB) until the process exits, used or not.
+//
+// Consequences the caller has to know:
+//   * a batch whose scratch need (ffemb_embed_backward_workspace_bytes) is
+//     larger than the array is refused with FFEMB_ERR_WORKSPACE_TOO_SMALL --
+//     at out_dim 128 that is roughly 250k lookups per call;
+//   * the first call on each device looks the array's device address up
+//     (cudaGetSymbolAddress, once per device, with that device current);
+//     make that first call outside any stream capture;
+//   * all calls on one device share the one array.  It still holds whatever
+//     the previous call left there; the only part that has to start from
+//     zero -- the two chain counters -- is cleared by every call on its
+//     stream before use.  Two calls that overlap on the GPU (different
+//     streams, or different host threads) would trample each other's keys
+//     and partial sums: serialise them.
+// Nothing here calls cudaMalloc, cudaFree or a library routine that does.
+// ---------------------------------------------------------------------------
+#define FFEMB_STATIC_SCRATCH_BYTES (8u << 20)
+
+// Lives in device memory; in host code this name is only a handle for
+// cudaGetSymbolAddress, never a pointer a kernel could be given.
+static __device__ __align__(256) unsigned char g_static_scratch[FFEMB_STATIC_SCRATCH_BYTES];
+
+namespace ffemb {
+
+constexpr int kMaxDevices = 64;
+static void *g_static_scratch_ptr[kMaxDevices];  // device address of the array, per device
+static std::atomic<bool> g_static_scratch_ready[kMaxDevices];
+
+// Device address of g_static_scratch on the current device (looked up once).
+static int static_scratch(void **ptr) {
+  int dev = -1;
+  FFEMB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(FFEMB_ERR_UNSUPPORTED, "backward_sgd_static: device ordinal out of range");
+  if (!g_static_scratch_ready[dev].load(std::memory_order_acquire)) {
+    void *p = nullptr;
+    FFEMB_CUDA_OK(cudaGetSymbolAddress(&p, g_static_scratch));
+    g_static_scratch_ptr[dev] = p;
+    g_static_scratch_ready[dev].store(true, std::memory_order_release);
+  }
+  *ptr = g_static_scratch_ptr[dev];
+  return FFEMB_OK;
+}
+
+}  // namespace ffemb
+
+extern "C" size_t ffemb_static_scratch_bytes(void) { return FFEMB_STATIC_SCRATCH_BYTES; }
+
+extern "C" int ffemb_embed_backward_sgd_static(const ffemb_lookup_t *lookups, int num_tables,
+                                               int batch, int out_dim, enum AggrMode aggr,
+                                               const ffemb_matrix_t *grad, float lr, int *err_flag,
+                                               void *stream) {
+  if (aggr != AGGR_MODE_SUM && aggr != AGGR_MODE_AVG)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "backward_sgd_static: aggr must be SUM or AVG");
+  if (int rc = check_lookups("backward_sgd_static", lookups, num_tables, batch, out_dim)) return rc;
+  if (num_tables > kMaxTables)
+    return fail(FFEMB_ERR_UNSUPPORTED, "backward_sgd_static: at most " + std::to_string(kMaxTables) +
+                                           " tables per call");
+  const Group g = group_of(lookups, num_tables);
+  const size_t need = carve(nullptr, g.n, g.total_entries, out_dim).total;
+  if (need > FFEMB_STATIC_SCRATCH_BYTES)
+    return fail(FFEMB_ERR_WORKSPACE_TOO_SMALL,
+                "backward_sgd_static: this batch (" + std::to_string(g.n) + " lookups, out_dim " +
+                    std::to_string(out_dim) + ") needs " + std::to_string(need) +
+                    " bytes of scratch, the built-in array has " +
+                    std::to_string(FFEMB_STATIC_SCRATCH_BYTES) +
+                    "; split the batch or use ffemb_embed_backward_sgd with your own workspace");
+  void *scratch = nullptr;
+  if (int rc = static_scratch(&scratch)) return rc;
+  return backward_impl(kSort | kUpdate, lookups, num_tables, batch, out_dim, aggr == AGGR_MODE_AVG,
+                       grad, lr, scratch, FFEMB_STATIC_SCRATCH_BYTES, err_flag, stream);
+}

@@ -117,6 +117,25 @@ def embed_backward_sgd(lookups, batch, out_dim, aggr, grad, lr, workspace, err_f
                                               C.byref(mat), lr, p, n, err, _stream_ptr(stream)))
 
 
+def embed_backward_sgd_static(lookups, batch, out_dim, aggr, grad, lr, err_flag=None, stream=None):
+    """ffemb_embed_backward_sgd_static: the same step without a workspace argument.
+
+    For hosts that are not allowed to allocate device memory (no cudaMalloc, no
+    torch.empty): the scratch is a fixed 8 MiB array inside libffemb.so.  Larger
+    batches raise FFEmbError(status 5).  Calls on one device share that array,
+    so run them one after the other on one stream; make the first call on a
+    device outside stream capture.
+    """
+    mat = grad if isinstance(grad, Matrix) else make_matrix(grad)
+    err = C.c_void_p(err_flag.data_ptr()) if err_flag is not None else None
+    check(_lib.lib().ffemb_embed_backward_sgd_static(lookups, len(lookups), batch, out_dim, int(aggr),
+                                                     C.byref(mat), lr, err, _stream_ptr(stream)))
+
+
+def static_scratch_bytes():
+    return _lib.lib().ffemb_static_scratch_bytes()
+
+
 def embed_backward_sort(lookups, batch, out_dim, workspace, err_flag=None, stream=None):
     err = C.c_void_p(err_flag.data_ptr()) if err_flag is not None else None
     p, n = _ws_ptr(workspace)

@@ -153,6 +153,31 @@ int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tables,
                            void *workspace, size_t workspace_bytes,
                            void *stream);
 
+/* ffemb_embed_backward_sgd for callers that cannot allocate device memory.
+ * (No counterpart in the reference, which allocates through Legion.)
+ * Some hosts of this library must not call cudaMalloc: a plugin inside a
+ * framework that owns the whole memory pool and lends no scratch, or a
+ * latency-critical loop that may not take the allocator's device-wide lock.
+ * This variant therefore takes no workspace: it uses a fixed array inside the
+ * library image -- ffemb_static_scratch_bytes() = 8 MiB of device memory that
+ * every GPU which loads the library keeps until the process exits.
+ *   - A batch needing more scratch than that (about 250k lookups at out_dim
+ *     128; ffemb_embed_backward_workspace_bytes gives the need) is refused
+ *     with FFEMB_ERR_WORKSPACE_TOO_SMALL.
+ *   - The first call on each device resolves the array's device address;
+ *     make that call before any stream capture begins.
+ *   - All calls on a device share the array and find the previous call's
+ *     data in it; the chain counters, the only part that must start at zero,
+ *     are cleared by each call.  Calls that overlap on the GPU race on the
+ *     array: issue them one after the other on one stream.
+ * Inputs, outputs and results are those of ffemb_embed_backward_sgd. */
+size_t ffemb_static_scratch_bytes(void);
+int ffemb_embed_backward_sgd_static(const ffemb_lookup_t *lookups,
+                                    int num_tables, int batch, int out_dim,
+                                    enum AggrMode aggr,
+                                    const ffemb_matrix_t *grad, float lr,
+                                    int *err_flag, void *stream);
+
 /* W[i] = (max-min) * u_i + min, u_i in (0,1] from a counter-based generator
  * keyed by (seed, i).  Stands in for UniformInitializer::init_task
  * (src/runtime/initializer_kernel.cu:24-85) + scale_kernel
