@@ -87,6 +87,13 @@ struct Model {
   cudaStream_t stream = nullptr;
   bool compiled = false;
   bool sorted = false;  // backward() ran since the last update()
+  // forward() starts the backward's key sort on a side stream (it needs only
+  // the indices), so that it runs under the bandwidth-bound gather
+  bool presort = true;
+  bool presorted = false;
+  std::vector<int64_t> presort_sig;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_inputs = nullptr, ev_sorted = nullptr;
   void *workspace = nullptr;
   size_t workspace_bytes = 0;
   int *err_dev = nullptr;
@@ -132,9 +139,10 @@ static std::vector<LaunchGroup> groups_of(Model *m, bool need_grad) {
 
 // lookups + matrix for one group; `grad` selects output-gradient buffers.
 static int describe(const LaunchGroup &g, bool grad, std::vector<ffemb_lookup_t> &lk,
-                    ffemb_matrix_t &mat) {
+                    ffemb_matrix_t &mat, bool indices_only = false) {
   float *base = nullptr;
   for (Op *op : g.ops) {
+    if (indices_only) break;
     float *p = (float *)(grad ? op->output->grad.ptr : op->output->data.ptr);
     if (!p)
       return fail(FFEMB_ERR_INVALID_ARGUMENT,
@@ -154,10 +162,11 @@ static int describe(const LaunchGroup &g, bool grad, std::vector<ffemb_lookup_t>
     l.num_entries = op->N;
     l.bag_size = op->input->dims[1];
     l.num_indices = (int64_t)op->input->dims[0] * l.bag_size;
-    l.col = p - base;
+    l.col = indices_only ? 0 : p - base;
     lk.push_back(l);
   }
   memset(&mat, 0, sizeof mat);
+  if (indices_only) return FFEMB_OK;
   mat.base[0] = base;
   mat.num_parts = 1;
   mat.rows_per_part = g.ops[0]->input->dims[0];
@@ -237,6 +246,9 @@ extern "C" void ffemb_model_destroy(ffemb_model_t h) {
     if (op->W) cudaFree(op->W);
   if (m->workspace) cudaFree(m->workspace);
   if (m->err_dev) cudaFree(m->err_dev);
+  if (m->side) cudaStreamDestroy(m->side);
+  if (m->ev_inputs) cudaEventDestroy(m->ev_inputs);
+  if (m->ev_sorted) cudaEventDestroy(m->ev_sorted);
   if (m->out_mat) cudaFree(m->out_mat);
   if (m->grad_mat) cudaFree(m->grad_mat);
   if (m->own_strategy) ffemb_strategy_destroy(m->strategy);
@@ -426,6 +438,13 @@ extern "C" int ffemb_model_compile(ffemb_model_t h) {
   }
   FFEMB_CUDA_OK(cudaMalloc(&m->err_dev, sizeof(int)));
   FFEMB_CUDA_OK(cudaMemsetAsync(m->err_dev, 0, sizeof(int), m->stream));
+  {
+    int lo = 0, hi = 0;  // numerically lowest value = highest priority
+    FFEMB_CUDA_OK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    FFEMB_CUDA_OK(cudaStreamCreateWithPriority(&m->side, cudaStreamNonBlocking, hi));
+  }
+  FFEMB_CUDA_OK(cudaEventCreateWithFlags(&m->ev_inputs, cudaEventDisableTiming));
+  FFEMB_CUDA_OK(cudaEventCreateWithFlags(&m->ev_sorted, cudaEventDisableTiming));
   m->compiled = true;
   return FFEMB_OK;
 }
@@ -441,34 +460,13 @@ static int ready(Model *m, const char *who) {
   return FFEMB_OK;
 }
 
-extern "C" int ffemb_model_forward(ffemb_model_t h) {
-  Model *m = M(h);
-  if (int rc = ready(m, "forward")) return rc;
-  std::vector<ffemb_lookup_t> lk;
-  ffemb_matrix_t mat;
-  for (const LaunchGroup &g : groups_of(m, false)) {
-    if (int rc = describe(g, false, lk, mat)) return rc;
-    if (int rc = ffemb_embed_forward(lk.data(), (int)lk.size(), m->cfg.batch_size, g.D,
-                                     (enum AggrMode)g.aggr, &mat, m->err_dev, m->stream))
-      return rc;
-  }
-  return FFEMB_OK;
-}
-
-extern "C" int ffemb_model_zero_gradients(ffemb_model_t h) {
-  Model *m = M(h);
-  if (int rc = ready(m, "zero_gradients")) return rc;
-  m->sorted = false;  // the (sparse) table gradient is now empty
-  return FFEMB_OK;
-}
-
 // Workspace region of each group, in groups_of() order.
-static int backward_phase(Model *m, bool sort, bool update) {
+static int backward_phase(Model *m, bool sort, bool update, cudaStream_t stream) {
   std::vector<ffemb_lookup_t> lk;
   ffemb_matrix_t mat;
   size_t off = 0;
   for (const LaunchGroup &g : groups_of(m, true)) {
-    if (int rc = describe(g, true, lk, mat)) return rc;
+    if (int rc = describe(g, true, lk, mat, /*indices_only=*/!update)) return rc;
     int64_t n = 0, e = 0;
     for (const ffemb_lookup_t &l : lk) {
       n += l.num_indices;
@@ -481,21 +479,84 @@ static int backward_phase(Model *m, bool sort, bool update) {
     off += need;
     if (sort)
       if (int rc = ffemb_embed_backward_sort(lk.data(), (int)lk.size(), m->cfg.batch_size, g.D, ws,
-                                             need, m->err_dev, m->stream))
+                                             need, m->err_dev, stream))
         return rc;
     if (update)
       if (int rc = ffemb_embed_sgd_update(lk.data(), (int)lk.size(), m->cfg.batch_size, g.D,
                                           (enum AggrMode)g.aggr, &mat, (float)m->opt->lr, ws, need,
-                                          m->stream))
+                                          stream))
         return rc;
   }
+  return FFEMB_OK;
+}
+
+// What the sorted keys in the workspace depend on: grouping and index buffers.
+static std::vector<int64_t> sort_signature(Model *m) {
+  std::vector<int64_t> sig;
+  for (const LaunchGroup &g : groups_of(m, true)) {
+    sig.push_back(-1);
+    sig.push_back(g.D);
+    sig.push_back(g.ld_out);
+    sig.push_back(g.ld_grad);
+    for (Op *op : g.ops) {
+      sig.push_back(op->index);
+      sig.push_back((int64_t)(uintptr_t)op->input->data.ptr);
+    }
+  }
+  return sig;
+}
+
+extern "C" int ffemb_model_forward(ffemb_model_t h) {
+  Model *m = M(h);
+  if (int rc = ready(m, "forward")) return rc;
+  // Training: fork the key sort of the coming backward onto the side stream.
+  // It reads only the index tensors, which are complete at this point of the
+  // model stream, and it is small and latency-bound, so it hides under the
+  // gather.  backward() joins it.
+  m->presorted = false;
+  // The sort goes first, on a high-priority stream: its small grids then get
+  // SM slots as they free up instead of queueing behind the gather's
+  // thousands of blocks.
+  const bool presort = m->presort && m->opt;
+  if (presort) {
+    FFEMB_CUDA_OK(cudaEventRecord(m->ev_inputs, m->stream));
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(m->side, m->ev_inputs, 0));
+    if (int rc = backward_phase(m, true, false, m->side)) return rc;
+    FFEMB_CUDA_OK(cudaEventRecord(m->ev_sorted, m->side));
+  }
+  std::vector<ffemb_lookup_t> lk;
+  ffemb_matrix_t mat;
+  for (const LaunchGroup &g : groups_of(m, false)) {
+    if (int rc = describe(g, false, lk, mat)) return rc;
+    if (int rc = ffemb_embed_forward(lk.data(), (int)lk.size(), m->cfg.batch_size, g.D,
+                                     (enum AggrMode)g.aggr, &mat, m->err_dev, m->stream))
+      return rc;
+  }
+  if (presort) {
+    // join right away in stream order: later work on the model stream (and a
+    // stream capture) sees one timeline; the kernels still overlap the gather
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, m->ev_sorted, 0));
+    m->presort_sig = sort_signature(m);
+    m->presorted = true;
+  }
+  return FFEMB_OK;
+}
+
+extern "C" int ffemb_model_zero_gradients(ffemb_model_t h) {
+  Model *m = M(h);
+  if (int rc = ready(m, "zero_gradients")) return rc;
+  m->sorted = false;  // the (sparse) table gradient is now empty
   return FFEMB_OK;
 }
 
 extern "C" int ffemb_model_backward(ffemb_model_t h) {
   Model *m = M(h);
   if (int rc = ready(m, "backward")) return rc;
-  if (int rc = backward_phase(m, true, false)) return rc;
+  if (m->presorted && m->presort_sig == sort_signature(m)) {
+    m->presorted = false;  // forward() already sorted these indices
+  } else {
+    if (int rc = backward_phase(m, true, false, m->stream)) return rc;
+  }
   m->sorted = true;
   return FFEMB_OK;
 }
@@ -509,7 +570,7 @@ extern "C" int ffemb_model_update(ffemb_model_t h) {
                 "update: the sparse fused SGD equals the reference's dense sgd_update only for "
                 "momentum == 0 and weight_decay == 0");
   if (!m->sorted) return FFEMB_OK;  // zero gradient: W -= lr*0
-  if (int rc = backward_phase(m, false, true)) return rc;
+  if (int rc = backward_phase(m, false, true, m->stream)) return rc;
   m->sorted = false;
   return FFEMB_OK;
 }

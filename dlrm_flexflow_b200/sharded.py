@@ -147,7 +147,7 @@ class ShardedEmbeddingBags(object):
                              update to this rank's tables.
     """
 
-    def __init__(self, plan, rank, bag, aggr, lr, exchange="p2p", group=None, init_seed=1234):
+    def __init__(self, plan, rank, bag, aggr, lr, exchange="p2p", group=None, init_seed=1234, presort=True):
         import torch
         import torch.distributed as dist
         from . import kernels
@@ -172,6 +172,13 @@ class ShardedEmbeddingBags(object):
         self.err = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._peers = []
+        # the backward's key sort needs only the indices: forward() runs it on a
+        # side stream underneath the gather (and its exchange)
+        self._presort = presort
+        self._sorted_for = None
+        # high priority: the sort's small grids take SM slots as they free up
+        # instead of queueing behind the gather's thousands of blocks
+        self._side = torch.cuda.Stream(priority=-1) if presort else None
         if exchange == "p2p" and N > 1:
             self._buf = _DeviceBuffer(2 * Bs * T * D)
             handles = [None] * N
@@ -225,9 +232,22 @@ class ShardedEmbeddingBags(object):
         return self.K.make_lookups(self.tables, indices, cols=self._cols)
 
     def forward(self, indices):
-        plan, K = self.plan, self.K
+        plan, K, torch = self.plan, self.K, self.torch
+        self._sorted_for = None
         if self.tables:
-            K.embed_forward(self._lookups(indices), plan.B, plan.D, self.aggr, self._out_mat, self.err)
+            lk = self._lookups(indices)
+            if self._presort:
+                main = torch.cuda.current_stream()
+                ready = torch.cuda.Event()
+                ready.record(main)
+                self._side.wait_event(ready)
+                K.embed_backward_sort(lk, plan.B, plan.D, self.workspace, self.err, stream=self._side)
+                done = torch.cuda.Event()
+                done.record(self._side)
+            K.embed_forward(lk, plan.B, plan.D, self.aggr, self._out_mat, self.err)
+            if self._presort:
+                main.wait_event(done)
+                self._sorted_for = [i.data_ptr() for i in indices]
         if plan.N > 1 and self.exchange == "nccl":
             self.dist.all_to_all_single(self._fwd_recv, self._fwd_send[:plan.N * plan.Bs * plan.width(self.rank)],
                                         plan.forward_recv_splits(self.rank),
@@ -247,8 +267,13 @@ class ShardedEmbeddingBags(object):
         else:
             self.barrier()      # every rank's self.grad is complete before peers read it
         if self.tables:
-            K.embed_backward_sgd(self._lookups(indices), plan.B, plan.D, self.aggr, self._grad_mat, self.lr,
-                                 self.workspace, self.err)
+            lk = self._lookups(indices)
+            if self._sorted_for == [i.data_ptr() for i in indices]:     # forward() sorted these already
+                K.embed_sgd_update(lk, plan.B, plan.D, self.aggr, self._grad_mat, self.lr, self.workspace)
+            else:
+                K.embed_backward_sgd(lk, plan.B, plan.D, self.aggr, self._grad_mat, self.lr, self.workspace,
+                                     self.err)
+            self._sorted_for = None
         if not (plan.N > 1 and self.exchange == "nccl"):
             self.barrier()      # peers are done reading self.grad / may overwrite self.out
 
