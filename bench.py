@@ -327,10 +327,18 @@ def run_ours(args, w):
                        "full_bytes": upd_bytes + n_lookups * D * 4 + n_lookups * 8},
     }
     dom = "sgd_update" if upd_ms >= fwd_ms else "forward"
-    roofline = {"bound": "hbm", "kernel": "reduce_l1_kernel (segment reduce + sparse SGD)" if dom == "sgd_update"
-                else "fwd_onehot/multihot_kernel (gather-and-pool)",
+    traffic = None
+    try:   # DRAM bytes per launch of that kernel from the committed ncu capture of this workload
+        if args.dist == "uniform":
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[w["name"]][dom]
+    except Exception:
+        traffic = None
+    roofline = {"bound": "hbm",
+                "kernel": "reduce_l1_kernel (segment reduce + sparse SGD; timed with its l2/l3 tails)"
+                if dom == "sgd_update" else "fwd_onehot/multihot_kernel (gather-and-pool; timed with the "
+                "overlapped key sort's join)",
                 "achieved": phases[dom]["gbs"], "peak": peak, "unit": "GB/s",
-                "frac": phases[dom]["gbs"] / peak, "peak_source": peak_src, "traffic": None,
+                "frac": phases[dom]["gbs"] / peak, "peak_source": peak_src, "traffic": traffic,
                 "achieved_full": phases[dom]["full_bytes"] / phases[dom]["ms"] / 1e6}
     line = {
         "metric": METRIC, "value": B / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,

@@ -14,7 +14,10 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libffemb.so")
+# FFEMB_VARIANT + FFEMB_NVCC_EXTRA build a tuning variant next to the default library
+VARIANT = os.environ.get("FFEMB_VARIANT", "")
+EXTRA = os.environ.get("FFEMB_NVCC_EXTRA", "").split()
+LIB = os.path.join(HERE, "libffemb%s.so" % VARIANT)
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -52,14 +55,14 @@ def build(force=False, verbose=False):
     """Compile every CUDA source into one shared library.  Returns its path."""
     if not force and not needs_build():
         return LIB
-    obj_dir = os.path.join(HERE, "build")
+    obj_dir = os.path.join(HERE, "build" + VARIANT)
     os.makedirs(obj_dir, exist_ok=True)
     nvcc = nvcc_path()
     objs, procs = [], []
     for src in sources():
         obj = os.path.join(obj_dir, os.path.basename(src) + ".o")
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-I", os.path.join(ROOT, "include"), "-I", CSRC,
+        cmd = [nvcc, *NVCC_FLAGS, *EXTRA, "-I", os.path.join(ROOT, "include"), "-I", CSRC,
                "-x", "cu", "-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                                             text=True)))

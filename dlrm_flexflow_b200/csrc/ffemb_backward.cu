@@ -29,8 +29,14 @@ namespace ffemb {
 
 constexpr int kChunk = 32;  // sorted positions per sub-warp in reduce_l1
 constexpr int kBwdThreads = 256;
-constexpr int kBU = 8;            // positions whose rows are in flight together
+#ifndef FFEMB_BU
+#define FFEMB_BU 8
+#endif
+constexpr int kBU = FFEMB_BU;     // positions whose rows are in flight together
 constexpr int kShortChain = 32;   // reduce_l2 sums chains up to this many partials itself
+#ifndef FFEMB_L1_MINBLOCKS
+#define FFEMB_L1_MINBLOCKS 2
+#endif
 
 struct KeyTable {  // make_keys view
   const int64_t *idx;
@@ -213,7 +219,7 @@ constexpr int kLeadCont = 2;  // ... and also continues past the end of the chun
 constexpr int kHasTrail = 4;  // last run started in the chunk and continues past it
 
 template <typename KeyT, int G, bool VEC>
-__global__ void __launch_bounds__(kBwdThreads, 2)
+__global__ void __launch_bounds__(kBwdThreads, FFEMB_L1_MINBLOCKS)
 reduce_l1_kernel(const __grid_constant__ BwdParams p) {
   constexpr int U = kBU;
   constexpr int S = kBwdThreads / G;  // chunks (sub-warps) per block
@@ -261,7 +267,14 @@ reduce_l1_kernel(const __grid_constant__ BwdParams p) {
       const int b = (int)(v - (uint32_t)t * (uint32_t)p.B);
       gptr[j] = matrix_row(p.grad, b) + tb.col;
       wptr[j] = tb.W + ((int64_t)k - tb.row_base) * D;
-      if (p.avg) glen[j] = tb.off ? (float)(int)(tb.off[b + 1] - tb.off[b]) : (float)tb.L;
+      if (p.avg) {
+        // per-position gradient is g / (float)len (reference embedding.cu:213-218).
+        // For len a power of two, g * (1/len) is the same correctly rounded
+        // value and costs one multiply: stored positive.  Otherwise keep the
+        // IEEE division: stored as -len.
+        const float len = tb.off ? (float)(int)(tb.off[b + 1] - tb.off[b]) : (float)tb.L;
+        glen[j] = (__float_as_uint(len) & 0x7FFFFFu) == 0 ? 1.0f / len : -len;
+      }
     }
     validbits |= ((__ballot_sync(0xffffffffu, valid) >> subshift) & gmask) << (j * G);
     headbits |= ((__ballot_sync(0xffffffffu, head) >> subshift) & gmask) << (j * G);
@@ -296,11 +309,18 @@ reduce_l1_kernel(const __grid_constant__ BwdParams p) {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
             const int q = base + u;
-            const float len = __shfl_sync(submask, glen[q / G], q % G, G);
-            gv[u].x /= len;
-            gv[u].y /= len;
-            gv[u].z /= len;
-            gv[u].w /= len;
+            const float sc = __shfl_sync(submask, glen[q / G], q % G, G);
+            if (sc > 0.f) {
+              gv[u].x *= sc;
+              gv[u].y *= sc;
+              gv[u].z *= sc;
+              gv[u].w *= sc;
+            } else {
+              gv[u].x /= -sc;
+              gv[u].y /= -sc;
+              gv[u].z /= -sc;
+              gv[u].w /= -sc;
+            }
           }
         }
 #pragma unroll
