@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N>1: fused peer-memory exchange inside the kernels, or NCCL all-to-all")
     ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balance"])
+    ap.add_argument("--no-graph", dest="graph", action="store_false",
+                    help="launch every kernel from the host each step instead of replaying CUDA graphs")
     return ap.parse_args()
 
 
@@ -63,53 +65,90 @@ def measured_peaks():
 # clocks during the timed region
 # ---------------------------------------------------------------------------
 class ClockSampler(object):
-    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons of one GPU, polled through NVML from a
+    thread while the timed region runs (in-process: nvidia-smi takes longer to
+    start than a short timed region lasts; it is the fallback)."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"),
+               (0x4, "sw_power_cap"))
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.samples, self.bits, self.max_mhz = index, [], 0, None
+        self._stop = threading.Event()
+        self.thread, self.nvml, self.handle, self.proc = None, None, None, None
+
+    def _nvml_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[self.index])
+            except Exception:
+                pass
+        return self.index
 
     def start(self):
+        if os.environ.get("FFEMB_NO_CLOCKS") == "1":
+            return
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self._nvml_index())
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.nvml = None
+            self._start_smi()
+
+    def _poll(self):
+        n = self.nvml
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+                try:
+                    self.bits |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:
+                    self.bits |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+            except Exception:
+                pass
+            self._stop.wait(0.01)
+
+    def _start_smi(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm,"
+                 "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
                  "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.lines = []
+            self.thread = threading.Thread(target=lambda: [self.lines.append(l.strip()) for l in self.proc.stdout],
+                                           daemon=True)
             self.thread.start()
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
-
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], None, set()
-        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for line in self.lines:
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0]))
-                mx = float(f[1])
-            except ValueError:
-                continue
-            for name, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self._stop.set()
+        reasons = []
+        if self.nvml is not None:
+            self.thread.join(timeout=1)
+            reasons = [name for bit, name in self.REASONS if self.bits & bit]
+        elif self.proc is not None:
+            self.proc.terminate()
+            for line in self.lines:
+                f = [x.strip() for x in line.split(",")]
+                try:
+                    self.samples.append(float(f[0]))
+                    self.max_mhz = float(f[1])
+                except (ValueError, IndexError):
+                    continue
+                reasons += [name for (_, name), v in zip(self.REASONS, f[2:6]) if v.lower().startswith("active")]
+        else:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML and no nvidia-smi"], "samples": 0}
+        sm = sorted(self.samples)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(set(reasons)), "samples": len(sm)}
 
 
 # ---------------------------------------------------------------------------
@@ -193,7 +232,7 @@ def run_reference_arm(args, w):
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, w, world):
@@ -202,6 +241,7 @@ def workload_config(args, w, world):
             "index_dist": args.dist if args.dist == "uniform" else "zipf(alpha=%g)" % args.alpha,
             "table_bytes": sum(w["rows"]) * w["dim"] * 4, "optimizer": "SGD lr=%g wd=0 momentum=0" % args.lr,
             "parallelism": "table-wise x%d" % world if world > 1 else "single GPU",
+            "launch": "cuda_graph_replay" if getattr(args, "graph", False) else "host_launches",
             "l2_policy": "inputs_larger_than_l2" if w["working_set"] > 2 * 126e6 else "l2_flush_between_steps"}
 
 
@@ -279,6 +319,47 @@ def run_ours(args, w):
         if ev:
             ev[3].record()
 
+    launches_per_step = None
+    if args.graph:
+        # The step as two CUDA graphs (forward | backward + update) over a fixed
+        # index buffer: the per-step host work is one small copy and two replays.
+        idx_static = torch.empty_like(pool[0])
+        for t in range(T):
+            ins[t].attach_torch(idx_static[t])
+        idx_static.copy_(pool[0])
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            m.set_stream(side.cuda_stream)
+            for _ in range(2):
+                m.forward(); m.zero_gradients(); m.backward(); m.update()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        l0 = kernels.kernel_launch_count()
+        g_fwd, g_bwd = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g_fwd):
+            m.set_stream(torch.cuda.current_stream().cuda_stream)
+            m.forward()
+        with torch.cuda.graph(g_bwd):
+            m.set_stream(torch.cuda.current_stream().cuda_stream)
+            m.zero_gradients()
+            m.backward()
+            m.update()
+        launches_per_step = kernels.kernel_launch_count() - l0      # kernels recorded in the two graphs
+        m.set_stream(stream.cuda_stream)
+
+        def step(p, ev=None):      # noqa: F811
+            if ev:
+                ev[0].record()
+            idx_static.copy_(pool[p])
+            g_fwd.replay()
+            if ev:
+                ev[1].record()
+                ev[2].record()
+            g_bwd.replay()
+            if ev:
+                ev[3].record()
+
     for i in range(max(args.warmup, 3)):
         step(i % args.pool)
         if flush is not None:
@@ -297,6 +378,8 @@ def run_ours(args, w):
             flush.zero_()
     torch.cuda.synchronize()
     launches = kernels.kernel_launch_count() - launches0
+    if launches_per_step is not None:
+        launches = launches_per_step * K      # replayed from the captured graphs
     clocks = sampler.stop()
     m.sync()   # surfaces an out-of-range index as an error
 
@@ -390,7 +473,7 @@ def run_ours(args, w):
         cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 def run_sharded(args, w, rank, world, local_rank):
@@ -408,7 +491,10 @@ def run_sharded(args, w, rank, world, local_rank):
         import dlrm_flexflow_b200 as ff
         owners = ff.balance_placement(rows, [B * L] * T, D, world, 150 << 30)
     plan = ShardPlan(rows, D, B, world, owners=owners)
-    sh = ShardedEmbeddingBags(plan, rank, L, aggr, args.lr, exchange=args.exchange)
+    sh = ShardedEmbeddingBags(plan, rank, L, aggr, args.lr, exchange=args.exchange,
+                              presort=os.environ.get("FFEMB_PRESORT", "1") == "1",
+                              barrier=os.environ.get("FFEMB_BARRIER", "peer"),
+                              backward_exchange=os.environ.get("FFEMB_BWD", "auto"))
     mine = plan.tables_of(rank)
     gen = torch.Generator(device="cuda")
     gen.manual_seed(4321 + rank)
@@ -426,6 +512,43 @@ def run_sharded(args, w, rank, world, local_rank):
         if ev:
             ev[2].record()
 
+    launches_per_step = None
+    if args.graph and args.exchange == "p2p":
+        # forward (+ its exchange and barrier) and backward (+ barriers) as two
+        # CUDA graphs over fixed index buffers; the peer barrier keeps its count
+        # on the device, so replays stay in step across ranks.
+        idx_static = [torch.empty_like(x) for x in pool[0]]
+        for d, x in zip(idx_static, pool[0]):
+            d.copy_(x)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                sh.forward(idx_static)
+                sh.backward_update(idx_static)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        dist.barrier()
+        l0 = kernels.kernel_launch_count()
+        g_fwd, g_bwd = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g_fwd):
+            sh.forward(idx_static)
+        with torch.cuda.graph(g_bwd):
+            sh.backward_update(idx_static)
+        launches_per_step = kernels.kernel_launch_count() - l0
+
+        def step(p, ev=None):      # noqa: F811
+            if ev:
+                ev[0].record()
+            for d, x in zip(idx_static, pool[p]):
+                d.copy_(x)
+            g_fwd.replay()
+            if ev:
+                ev[1].record()
+            g_bwd.replay()
+            if ev:
+                ev[2].record()
+
     for i in range(max(args.warmup, 3)):
         step(i % args.pool)
     sh.check_errors()
@@ -436,11 +559,18 @@ def run_sharded(args, w, rank, world, local_rank):
     launches0 = kernels.kernel_launch_count()
     dist.barrier()
     torch.cuda.synchronize()
+    if os.environ.get("FFEMB_TRACE") == "1" and launches_per_step is None:
+        sh.trace = []
     for i in range(K):
         step((args.warmup + i) % args.pool, evs[i])
     torch.cuda.synchronize()
+    if sh.trace is not None:
+        sys.stderr.write("TRACE rank %d (%d tables): %s\n" % (rank, len(mine), sh.trace_summary()))
+        sh.trace = None
     dist.barrier()
     launches = kernels.kernel_launch_count() - launches0
+    if launches_per_step is not None:
+        launches = launches_per_step * K      # replayed from the captured graphs
     clocks = sampler.stop()
     sh.check_errors()
     t = torch.tensor([evs[0][0].elapsed_time(evs[-1][2]),
@@ -511,13 +641,27 @@ def run_sharded(args, w, rank, world, local_rank):
                        "note": "bytes are per rank; every rank copies its own slice"}
     sh.close()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     dist.barrier()
     dist.destroy_process_group()
 
 
+_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line, on the real stdout."""
+    os.write(_STDOUT if _STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _STDOUT
     args = parse_args()
+    # Libraries (NCCL prints its version banner) write to fd 1: point it at
+    # stderr for the run and keep the real stdout for the JSON line alone.
+    sys.stdout.flush()
+    _STDOUT = os.dup(1)
+    os.dup2(2, 1)
     from dlrm_flexflow_b200 import workloads
     w = dict(workloads.WORKLOADS[args.config])
     w["name"] = args.config

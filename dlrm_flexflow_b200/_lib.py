@@ -41,6 +41,11 @@ class Matrix(C.Structure):
                 ("rows_per_part", C.c_int32), ("ld", C.c_int64)]
 
 
+class Push(C.Structure):
+    """ffemb_push_t"""
+    _fields_ = [("dst", C.c_void_p), ("dst_ld", C.c_int64), ("src_col", C.c_int64)]
+
+
 class Handle(C.Structure):
     """Every FFEMB_NEW_OPAQUE_TYPE: struct { void *impl; }"""
     _fields_ = [("impl", C.c_void_p)]
@@ -73,6 +78,8 @@ SIGNATURES = {
     "ffemb_ipc_get_handle": (_i, [_vp, _vp]),
     "ffemb_ipc_open_handle": (_i, [_vp, C.POINTER(C.c_void_p)]),
     "ffemb_ipc_close_handle": (_i, [_vp]),
+    "ffemb_peer_barrier": (_i, [C.POINTER(C.c_void_p), _i, _i, _vp, _vp]),
+    "ffemb_push_columns": (_i, [C.POINTER(Push), _i, _i, _i, _vp, _i64, _vp]),
     # config
     "ffemb_config_create": (_H, []),
     "ffemb_config_destroy": (None, [_H]),

@@ -46,3 +46,179 @@ extern "C" int ffemb_ipc_close_handle(void *device_ptr) {
   if (device_ptr) FFEMB_CUDA_OK(cudaIpcCloseMemHandle(device_ptr));
   return FFEMB_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Stream-ordered barrier among the ranks of one box, over peer memory.
+// Every rank owns FFEMB_BARRIER_WORDS 32-bit words, zeroed once: word q < world
+// is the flag written by rank q, word 16 is this rank's barrier count.  The
+// kernel bumps the count to `epoch` (kept on the device, so a captured launch
+// can be replayed), thread q stores `epoch` into peer q's flag[rank] (an
+// NVLink store) and then waits until its own flag[q] has reached `epoch`.
+// Everything a rank launched before the barrier on this stream has completed
+// when its barrier kernel starts, so after the barrier every peer's earlier
+// kernels -- and their stores into this rank's memory -- are done.  About two
+// NVLink latencies instead of a NCCL all-reduce.  The ranks run on different
+// GPUs, so the kernels are co-resident by construction; a peer that never
+// arrives trips the timeout and raises the error flag instead of hanging.
+// ---------------------------------------------------------------------------
+namespace ffemb {
+
+constexpr int kEpochWord = 16;
+
+struct BarrierParams {
+  uint32_t *flags[kMaxParts];  // flags[q] = base of rank q's words
+  int rank, world;
+  int *err;
+  unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void __launch_bounds__(32) peer_barrier_kernel(const __grid_constant__ BarrierParams p) {
+  const int q = threadIdx.x;
+  uint32_t epoch = 0;
+  if (q == 0) {
+    epoch = p.flags[p.rank][kEpochWord] + 1;
+    p.flags[p.rank][kEpochWord] = epoch;
+  }
+  epoch = __shfl_sync(0xffffffffu, epoch, 0);
+  if (q >= p.world) return;
+  __threadfence_system();
+  // release store into the peer's memory
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags[q] + p.rank), "r"(epoch) : "memory");
+  const uint32_t *mine = p.flags[p.rank] + q;
+  const unsigned long long t0 = globaltimer_ns();
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+    if ((int32_t)(v - epoch) >= 0) break;  // counts only grow
+    if (globaltimer_ns() - t0 > p.timeout_ns) {
+      if (p.err) *p.err = FFEMB_ERR_COMM;
+      break;
+    }
+    __nanosleep(64);
+  }
+}
+
+}  // namespace ffemb
+
+extern "C" int ffemb_peer_barrier(uint32_t *const *peer_flags, int rank, int world, int *err_flag,
+                                  void *stream) {
+  if (!peer_flags || world < 1 || world > kMaxParts || rank < 0 || rank >= world)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "peer_barrier: bad arguments");
+  BarrierParams p;
+  for (int q = 0; q < kMaxParts; ++q) p.flags[q] = q < world ? peer_flags[q] : nullptr;
+  for (int q = 0; q < world; ++q)
+    if (!p.flags[q]) return fail(FFEMB_ERR_INVALID_ARGUMENT, "peer_barrier: NULL flag pointer");
+  p.rank = rank;
+  p.world = world;
+  p.err = err_flag;
+  p.timeout_ns = 5ull * 1000 * 1000 * 1000;
+  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(p);
+  FFEMB_LAUNCH_OK("peer_barrier");
+  return FFEMB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Backward exchange as a push: every rank holds the upstream gradient of its
+// own samples for ALL tables, [B/N][T*D]; table t's owner needs the gradient
+// of all samples.  One kernel copies each table's column block straight into
+// its owner's staging matrix [B][T_owner*D] (rows rank*B/N ..) through the peer
+// mapping -- remote stores are fire-and-forget, unlike remote loads they do
+// not tie up the SM for a round trip -- so the update kernel then reads local
+// memory only.  Stands in for the gradient half of the reference's implicit
+// repartition at Concat (src/ops/concat.cu:263-320 add_with_stride + Legion
+// copies through zero-copy memory, src/ops/embedding.cu:343-347).
+// ---------------------------------------------------------------------------
+namespace ffemb {
+
+struct PushItem {
+  float *dst;
+  int64_t dst_ld;
+  int64_t src_col;
+};
+
+struct PushParams {
+  PushItem it[kMaxTables];
+  const float *src;
+  int64_t src_ld;
+  int rows;
+  int width;
+};
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) push_columns_kernel(const __grid_constant__ PushParams p) {
+  const PushItem &it = p.it[blockIdx.y];
+  const int per_row = VEC ? p.width / 4 : p.width;  // elements of this thread type per row
+  const int64_t total = (int64_t)p.rows * per_row;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  constexpr int U = 4;
+  for (int64_t i0 = (int64_t)blockIdx.x * 256 + threadIdx.x; i0 < total; i0 += stride * U) {
+    if (VEC) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < total) {
+          const int64_t r = i / per_row, c = (i - r * per_row) * 4;
+          v[u] = ld_row_nc(p.src + r * p.src_ld + it.src_col + c);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < total) {
+          const int64_t r = i / per_row, c = (i - r * per_row) * 4;
+          st_row(it.dst + r * it.dst_ld + c, v[u]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < total) {
+          const int64_t r = i / per_row, c = i - r * per_row;
+          it.dst[r * it.dst_ld + c] = __ldg(p.src + r * p.src_ld + it.src_col + c);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace ffemb
+
+extern "C" int ffemb_push_columns(const ffemb_push_t *items, int num_items, int rows, int width,
+                                  const float *src, int64_t src_ld, void *stream) {
+  if (!items || num_items < 0 || rows < 0 || width <= 0 || !src)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "push_columns: bad arguments");
+  if (num_items == 0 || rows == 0) return FFEMB_OK;
+  bool vec = width % 4 == 0 && src_ld % 4 == 0 && ((uintptr_t)src & 15) == 0;
+  for (int i = 0; i < num_items; ++i) {
+    if (!items[i].dst) return fail(FFEMB_ERR_INVALID_ARGUMENT, "push_columns: NULL destination");
+    vec = vec && ((uintptr_t)items[i].dst & 15) == 0 && items[i].dst_ld % 4 == 0 && items[i].src_col % 4 == 0;
+  }
+  PushParams p;
+  p.src = src;
+  p.src_ld = src_ld;
+  p.rows = rows;
+  p.width = width;
+  for (int i0 = 0; i0 < num_items; i0 += kMaxTables) {
+    const int n = num_items - i0 < kMaxTables ? num_items - i0 : kMaxTables;
+    for (int i = 0; i < n; ++i) p.it[i] = PushItem{items[i0 + i].dst, items[i0 + i].dst_ld, items[i0 + i].src_col};
+    const int64_t work = (int64_t)rows * (vec ? width / 4 : width);
+    int64_t bx = (work + 256 * 4 - 1) / (256 * 4);
+    // the copy is NVLink-bound: a few CTAs per SM are plenty (148 SMs)
+    if (bx > 148 * 4) bx = 148 * 4;
+    dim3 grid((unsigned)bx, n);
+    if (vec)
+      push_columns_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    else
+      push_columns_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    FFEMB_LAUNCH_OK("push_columns");
+  }
+  return FFEMB_OK;
+}

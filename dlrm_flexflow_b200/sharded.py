@@ -11,11 +11,16 @@ src/ops/concat.cu:159-215), and produces the gradient in the same layout.
 Two exchanges per step (the reference does them implicitly by Legion DMA
 through zero-copy host memory, src/ops/embedding.cu:280-284,343-347):
 
-  exchange="p2p"   fused: the forward kernel stores each pooled row straight
-                   into the consuming rank's [B/N][T*D] matrix over NVLink and
-                   the update kernel loads each gradient row straight from the
-                   producing rank's (peer mappings by CUDA IPC).  No staging
-                   buffer, no separate exchange pass, concat layout for free.
+  exchange="p2p"   over peer memory (CUDA IPC mappings), both directions as
+                   NVLink STORES (fire-and-forget; remote loads cost the SM a
+                   round trip each and measured about half the bandwidth):
+                   forward -- the gather kernel stores each pooled row straight
+                   into the consuming rank's [B/N][T*D] matrix (fused, concat
+                   layout for free); backward -- one push kernel copies every
+                   table's gradient block into its owner's [B][T_r*D] staging
+                   matrix, under which the key sort runs on a side stream; the
+                   update then reads local memory only.  Ordering between
+                   ranks: two ffemb_peer_barrier kernels per step.
   exchange="nccl"  baseline: kernels write/read local staging buffers and
                    NCCL all-to-all (all_to_all_single with uneven splits)
                    moves them; a strided copy builds / splits the concat
@@ -145,9 +150,16 @@ class ShardedEmbeddingBags(object):
     backward_update(indices) consumes self.grad ([B/N][T*D], filled by the
                              caller) on every rank and applies the sparse SGD
                              update to this rank's tables.
+
+    Hazards between steps are covered by the two barriers of a step: peers
+    overwrite this rank's `out` only in their next forward, which they reach
+    after the backward barrier that this rank passes only after it has used
+    `out`; peers overwrite the gradient staging only in their next push, after
+    the forward barrier that this rank passes only after its update.
     """
 
-    def __init__(self, plan, rank, bag, aggr, lr, exchange="p2p", group=None, init_seed=1234, presort=True):
+    def __init__(self, plan, rank, bag, aggr, lr, exchange="p2p", group=None, init_seed=1234, presort=True,
+                 barrier="peer", backward_exchange="auto"):
         import torch
         import torch.distributed as dist
         from . import kernels
@@ -160,27 +172,48 @@ class ShardedEmbeddingBags(object):
         self.plan, self.rank, self.bag, self.aggr, self.lr = plan, rank, bag, aggr, lr
         self.exchange, self.group, self.K, self.torch, self.dist = exchange, group, kernels, torch, dist
         self.tables_idx = plan.tables_of(rank)
-        D, Bs, T, N = plan.D, plan.Bs, plan.T, plan.N
+        D, Bs, T, N, B = plan.D, plan.Bs, plan.T, plan.N, plan.B
         self.tables = []
         for t in self.tables_idx:
             w = torch.empty((plan.rows[t], D), device="cuda")
             r = (1.0 / plan.rows[t]) ** 0.5
             kernels.uniform_init(w, init_seed + t, -r, r)
             self.tables.append(w)
-        n_lookups = len(self.tables_idx) * plan.B * bag
+        n_lookups = len(self.tables_idx) * B * bag
         self.workspace = kernels.alloc_workspace(max(n_lookups, 1), sum(plan.rows[t] for t in self.tables_idx) + 1, D)
         self.err = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._peers = []
-        # the backward's key sort needs only the indices: forward() runs it on a
-        # side stream underneath the gather (and its exchange)
+        self._peer_flags = None
+        self._push = None
+        self.barrier_impl = barrier      # "peer": ffemb_peer_barrier kernel; "nccl": 4-byte all-reduce
+        # p2p backward exchange.  "push": gradient blocks are stored into the owners' staging, the
+        # update reads local memory.  "pull": the update kernel loads gradient rows from the peers
+        # while it works (no staging pass, but remote loads reach only about half the NVLink rate).
+        # Measured on C3: pull wins at N = 2 (0.80 vs 0.88 ms/step), push from N = 4 up.
+        if backward_exchange not in ("auto", "push", "pull"):
+            raise ValueError("backward_exchange must be 'auto', 'push' or 'pull'")
+        self.bwd_mode = backward_exchange if backward_exchange != "auto" else ("push" if plan.N >= 4 else "pull")
+        self.trace = None                # set to [] to collect per-call CUDA events (development aid)
+        # The backward's key sort needs only the indices.  It runs on a
+        # high-priority side stream (its small grids then take SM slots as they
+        # free up): under the gather when there is one GPU, under the
+        # NVLink-bound gradient push when there are several.
         self._presort = presort
         self._sorted_for = None
-        # high priority: the sort's small grids take SM slots as they free up
-        # instead of queueing behind the gather's thousands of blocks
         self._side = torch.cuda.Stream(priority=-1) if presort else None
+        self.grad = None
+        w_me = plan.width(rank)
         if exchange == "p2p" and N > 1:
-            self._buf = _DeviceBuffer(2 * Bs * T * D)
+            # one IPC-exportable allocation:
+            # [ out Bs x T*D | 64 barrier words | grad Bs x T*D | staging B x T_r*D (push mode) ]
+            off_flags = Bs * T * D
+            off_grad = off_flags + 64
+            off_stage = off_grad + Bs * T * D
+            self._buf = _DeviceBuffer(off_stage + (B * max(w_me, 4) if self.bwd_mode == "push" else 0))
+            self._buf.tensor[off_flags:off_stage].zero_()
+            self.grad = self._buf.tensor[off_grad:off_stage].view(Bs, T * D)
+            torch.cuda.synchronize()
             handles = [None] * N
             dist.all_gather_object(handles, self._buf.handle(), group=group)
             base = []
@@ -194,10 +227,25 @@ class ShardedEmbeddingBags(object):
                     self._peers.append(p.value)
                     base.append(p.value)
             self.out = self._buf.tensor[:Bs * T * D].view(Bs, T * D)
-            self.grad = self._buf.tensor[Bs * T * D:].view(Bs, T * D)
+            self._peer_flags = (C.c_void_p * N)(*[b + off_flags * 4 for b in base])
             self._out_mat = kernels.make_matrix(([b for b in base], T * D), rows_per_part=Bs)
-            self._grad_mat = kernels.make_matrix(([b + Bs * T * D * 4 for b in base], T * D), rows_per_part=Bs)
-            self._cols = [plan.global_col(t) for t in self.tables_idx]
+            self._out_cols = [plan.global_col(t) for t in self.tables_idx]
+            # backward: table t's block of my gradient goes to rows [rank*Bs, ..) of owner(t)'s staging
+            items = (_lib.Push * T)()
+            for t in range(T):
+                q = plan.owner[t]
+                wq = plan.width(q)
+                items[t].dst = base[q] + (off_stage + rank * Bs * wq + plan.local_col(t)) * 4
+                items[t].dst_ld = wq
+                items[t].src_col = plan.global_col(t)
+            if self.bwd_mode == "push":
+                self._push = items
+                self._grad_mat = kernels.make_matrix(([self._buf.ptr + off_stage * 4], max(w_me, 4)),
+                                                     rows_per_part=B)
+                self._grad_cols = [plan.local_col(t) for t in self.tables_idx]
+            else:
+                self._grad_mat = kernels.make_matrix(([b + off_grad * 4 for b in base], T * D), rows_per_part=Bs)
+                self._grad_cols = self._out_cols
         else:
             self._buf = None
             self.out = torch.zeros((Bs, T * D), device="cuda")
@@ -205,9 +253,9 @@ class ShardedEmbeddingBags(object):
             if N == 1:
                 self._out_mat = kernels.make_matrix(self.out)
                 self._grad_mat = kernels.make_matrix(self.grad)
-                self._cols = [plan.global_col(t) for t in self.tables_idx]
+                self._out_cols = self._grad_cols = [plan.global_col(t) for t in self.tables_idx]
             else:
-                w = plan.width(rank)
+                w = w_me
                 self._fwd_send = torch.empty(N * Bs * max(w, 1), device="cuda")
                 self._fwd_recv = torch.empty(Bs * T * D, device="cuda")
                 self._bwd_send = torch.empty(Bs * T * D, device="cuda")
@@ -218,35 +266,69 @@ class ShardedEmbeddingBags(object):
                 ptr = self._bwd_recv.data_ptr()
                 self._grad_mat = kernels.make_matrix(([ptr + q * Bs * w * 4 for q in range(N)], max(w, 4)),
                                                      rows_per_part=Bs)
-                self._cols = [plan.local_col(t) for t in self.tables_idx]
-        self.barrier()
+                self._out_cols = self._grad_cols = [plan.local_col(t) for t in self.tables_idx]
+        if N > 1:   # every rank's buffers and zeroed flags exist before any peer touches them
+            torch.cuda.synchronize()
+            dist.all_reduce(self._flag, group=group)
+            torch.cuda.synchronize()
 
     # -- stream-ordered cross-rank barrier (no host sync) ---------------------------
     def barrier(self):
-        if self.plan.N > 1:
+        if self.plan.N <= 1:
+            return
+        if self._peer_flags is not None and self.barrier_impl == "peer":   # own NVLink barrier kernel
+            check(lib().ffemb_peer_barrier(self._peer_flags, self.rank, self.plan.N,
+                                           C.c_void_p(self.err.data_ptr()),
+                                           C.c_void_p(self.torch.cuda.current_stream().cuda_stream)))
+        else:
             self.dist.all_reduce(self._flag, group=self.group)
 
-    def _lookups(self, indices):
+    def _mark(self, name):
+        if self.trace is not None:
+            ev = self.torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.trace.append((name, ev))
+
+    def trace_summary(self):
+        """Mean device time between consecutive marks, by (from, to) pair, in us."""
+        self.torch.cuda.synchronize()
+        acc = {}
+        for (a, ea), (b, eb) in zip(self.trace[:-1], self.trace[1:]):
+            k = a + " -> " + b
+            tot, n = acc.get(k, (0.0, 0))
+            acc[k] = (tot + ea.elapsed_time(eb) * 1e3, n + 1)
+        return {k: round(t / n, 1) for k, (t, n) in acc.items()}
+
+    def _lookups(self, indices, cols):
         if len(indices) != len(self.tables):
             raise ValueError("expected indices for %d local tables" % len(self.tables))
-        return self.K.make_lookups(self.tables, indices, cols=self._cols)
+        return self.K.make_lookups(self.tables, indices, cols=cols)
+
+    def _fork_sort(self, lk):
+        """Start the key sort on the side stream; returns the event to join on."""
+        torch, plan = self.torch, self.plan
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
+        self._side.wait_event(ready)
+        self.K.embed_backward_sort(lk, plan.B, plan.D, self.workspace, self.err, stream=self._side)
+        done = torch.cuda.Event()
+        done.record(self._side)
+        return done
 
     def forward(self, indices):
         plan, K, torch = self.plan, self.K, self.torch
         self._sorted_for = None
+        self._mark("fwd_begin")
         if self.tables:
-            lk = self._lookups(indices)
-            if self._presort:
-                main = torch.cuda.current_stream()
-                ready = torch.cuda.Event()
-                ready.record(main)
-                self._side.wait_event(ready)
-                K.embed_backward_sort(lk, plan.B, plan.D, self.workspace, self.err, stream=self._side)
-                done = torch.cuda.Event()
-                done.record(self._side)
+            lk = self._lookups(indices, self._out_cols)
+            done = None
+            if self._presort and plan.N == 1:
+                done = self._fork_sort(lk)
             K.embed_forward(lk, plan.B, plan.D, self.aggr, self._out_mat, self.err)
-            if self._presort:
-                main.wait_event(done)
+            self._mark("fwd_kernel_done")
+            if done is not None:
+                torch.cuda.current_stream().wait_event(done)
                 self._sorted_for = [i.data_ptr() for i in indices]
         if plan.N > 1 and self.exchange == "nccl":
             self.dist.all_to_all_single(self._fwd_recv, self._fwd_send[:plan.N * plan.Bs * plan.width(self.rank)],
@@ -255,37 +337,53 @@ class ShardedEmbeddingBags(object):
             plan.unpack_forward(self._fwd_recv, self.out)
         else:
             self.barrier()      # every rank's rows have landed in self.out
+        self._mark("fwd_end")
         return self.out
 
     def backward_update(self, indices):
-        plan, K = self.plan, self.K
+        plan, K, torch = self.plan, self.K, self.torch
+        lk = self._lookups(indices, self._grad_cols) if self.tables else None
+        done = None
+        presorted = lk is not None and self._sorted_for == [i.data_ptr() for i in indices]
+        if lk is not None and self._presort and not presorted and plan.N > 1:
+            done = self._fork_sort(lk)              # runs under the exchange below
         if plan.N > 1 and self.exchange == "nccl":
             plan.pack_backward(self.grad, self._bwd_send)
             self.dist.all_to_all_single(self._bwd_recv[:plan.N * plan.Bs * plan.width(self.rank)], self._bwd_send,
                                         plan.backward_recv_splits(self.rank),
                                         plan.backward_send_splits(self.rank), group=self.group)
-        else:
-            self.barrier()      # every rank's self.grad is complete before peers read it
-        if self.tables:
-            lk = self._lookups(indices)
-            if self._sorted_for == [i.data_ptr() for i in indices]:     # forward() sorted these already
+        elif plan.N > 1:
+            if self._push is not None:
+                check(lib().ffemb_push_columns(self._push, plan.T, plan.Bs, plan.D,
+                                               C.c_void_p(self.grad.data_ptr()), self.grad.stride(0),
+                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+                self._mark("push_done")
+            self.barrier()      # push: blocks have landed in the owners' staging; pull: every grad is complete
+        self._mark("bwd_exchange_done")
+        if lk is not None:
+            if done is not None:
+                torch.cuda.current_stream().wait_event(done)
+                presorted = True
+            if presorted:
                 K.embed_sgd_update(lk, plan.B, plan.D, self.aggr, self._grad_mat, self.lr, self.workspace)
             else:
                 K.embed_backward_sgd(lk, plan.B, plan.D, self.aggr, self._grad_mat, self.lr, self.workspace,
                                      self.err)
             self._sorted_for = None
-        if not (plan.N > 1 and self.exchange == "nccl"):
-            self.barrier()      # peers are done reading self.grad / may overwrite self.out
+        self._mark("bwd_end")
 
     def check_errors(self):
         self.torch.cuda.synchronize()
         e = int(self.err.item())
         if e:
             self.err.zero_()
-            raise _lib.FFEmbError(e, "an embedding index was outside [0, num_entries)")
+            raise _lib.FFEmbError(e, "a peer rank did not reach a barrier within 5 s" if e == _lib.FFEMB_ERR_COMM
+                                  else "an embedding index was outside [0, num_entries)")
 
     def close(self):
         self.torch.cuda.synchronize()
+        if self.plan.N > 1:
+            self.dist.barrier(group=self.group)      # nobody unmaps memory a peer may still write
         for p in self._peers:
             lib().ffemb_ipc_close_handle(p)
         self._peers = []

@@ -200,6 +200,32 @@ int ffemb_device_free(void *ptr);
 int ffemb_ipc_get_handle(void *device_ptr, uint8_t handle[64]);
 int ffemb_ipc_open_handle(const uint8_t handle[64], void **device_ptr);
 int ffemb_ipc_close_handle(void *device_ptr);
+/* Stream-ordered barrier among the `world` ranks of one box through peer
+ * memory: peer_flags[q] (HOST array of device pointers) is the mapped base of
+ * rank q's 32 zero-initialised uint32 words (word r < world: flag written by
+ * rank r; word 16: rank q's own barrier count, kept on the device so that a
+ * captured launch can be replayed).  All ranks must call it the same number
+ * of times.  After it, everything every peer enqueued before ITS barrier has
+ * completed.  A peer that does not arrive within 5 s sets
+ * *err_flag = FFEMB_ERR_COMM instead of hanging. */
+int ffemb_peer_barrier(uint32_t *const *peer_flags, int rank, int world,
+                       int *err_flag, void *stream);
+/* Backward exchange as a push.  A rank holds the upstream gradient of its own
+ * samples for all tables, src = [rows][src_ld]; item i copies the column block
+ * [src_col, src_col + width) of every row to dst + row*dst_ld, where dst is
+ * (a peer mapping of) the owning rank's staging matrix, already advanced to
+ * this rank's first sample and the table's first column.  Stands in for the
+ * gradient half of the reference's repartition at Concat
+ * (src/ops/concat.cu:263-320, src/ops/embedding.cu:343-347).  `items` is a
+ * HOST array. */
+typedef struct ffemb_push_t {
+  float *dst;
+  int64_t dst_ld;
+  int64_t src_col;
+} ffemb_push_t;
+int ffemb_push_columns(const ffemb_push_t *items, int num_items, int rows,
+                       int width, const float *src, int64_t src_ld,
+                       void *stream);
 
 /* ------------------------------------------------------------------------
  * (M) Model-level entry points (flexflow_c.h surface for this path)

@@ -25,12 +25,12 @@ def _problem(seed, T=5, D=64, B=256, L=2):
     return rows, D, B, L, idx, g
 
 
-def _run_rank(rank, world, exchange, owners, seed, lr=0.05, aggr=22):
+def _run_rank(rank, world, exchange, owners, seed, lr=0.05, aggr=22, bwd="auto"):
     from oracle import oracle as O
     from dlrm_flexflow_b200.sharded import ShardPlan, ShardedEmbeddingBags
     rows, D, B, L, idx, g = _problem(seed)
     plan = ShardPlan(rows, D, B, world, owners=owners)
-    sh = ShardedEmbeddingBags(plan, rank, L, aggr, lr, exchange=exchange)
+    sh = ShardedEmbeddingBags(plan, rank, L, aggr, lr, exchange=exchange, backward_exchange=bwd)
     mine = plan.tables_of(rank)
     W0 = {t: sh.tables[i].cpu().numpy() for i, t in enumerate(mine)}
     for t in mine:                                   # initialiser parity
@@ -73,23 +73,23 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, exchange, owners, seed):
+def _worker(rank, world, port, exchange, owners, seed, bwd):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        _run_rank(rank, world, exchange, owners, seed)
+        _run_rank(rank, world, exchange, owners, seed, bwd=bwd)
         dist.barrier()
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange", ["p2p", "nccl"])
+@pytest.mark.parametrize("exchange,bwd", [("p2p", "pull"), ("p2p", "push"), ("nccl", "auto")])
 @pytest.mark.parametrize("owners", [[0, 1, 0, 1, 0], [1, 1, 1, 1, 0]])
-def test_world2_nccl(exchange, owners):
+def test_world2_nccl(exchange, bwd, owners):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
-    mp.spawn(_worker, args=(2, _free_port(), exchange, owners, 9), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), exchange, owners, 9, bwd), nprocs=2, join=True)
