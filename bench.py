@@ -46,9 +46,13 @@ def parse_args():
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N>1: fused peer-memory exchange inside the kernels, or NCCL all-to-all")
     ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balance"])
-    ap.add_argument("--no-graph", dest="graph", action="store_false",
-                    help="launch every kernel from the host each step instead of replaying CUDA graphs")
-    return ap.parse_args()
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
+                    help="replay the step from CUDA graphs.  auto: where the step is launch-bound -- the small "
+                         "workloads on one GPU, and every sharded run; the big one-GPU steps are GPU-bound and "
+                         "overlap the key sort with the gather better when launched from the host")
+    ap.add_argument("--no-graph", dest="graph", action="store_const", const="off")
+    args = ap.parse_args()
+    return args
 
 
 def measured_peaks():
@@ -667,6 +671,9 @@ def main():
     w["name"] = args.config
     n = len(w["rows"]) * w["batch"] * w["bag"]
     w["working_set"] = min(sum(w["rows"]), n) * w["dim"] * 4 * 2 + n * w["dim"] * 4 // max(w["bag"], 1)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    small = w["working_set"] <= 2 * 126e6
+    args.graph = args.graph == "on" or (args.graph == "auto" and (world > 1 or small))
     if args.impl == "reference":
         run_reference_arm(args, w)
     else:
