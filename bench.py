@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--alpha", type=float, default=0.0)
     ap.add_argument("--pool", type=int, default=8, help="pre-generated index batches to rotate through")
     ap.add_argument("--lr", type=float, default=0.01)
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-row-cap", type=int, default=2_000_000)
@@ -438,40 +438,77 @@ def run_ours(args, w):
         "phases": phases, "clocks": clocks, "gpu_launches": int(launches),
     }
 
-    # ---- end to end: host buffers in, host buffers out, through the public API
+    # ---- end to end: host buffers in, host buffers out, through the public API.
+    # Every step copies its indices and upstream gradients from pinned host memory
+    # and its pooled outputs back.  The device-side staging is double-buffered and
+    # the copies run on their own streams, so step i's compute overlaps the H2D of
+    # step i+1 and the D2H of step i-1 (PCIe is full duplex); the host picks up
+    # the result of step i-1 before it issues step i+1.
     if not args.no_e2e:
+        m.set_stream(stream.cuda_stream)
         idx_host = pool[0].cpu().pin_memory()
         grad_host = torch.empty((B, T * D), pin_memory=True)
         grad_host.copy_(grad)
         out_host = torch.empty((B, T * D), pin_memory=True)
-        idx_dev = torch.empty_like(pool[0])
-        for t in range(T):
-            ins[t].attach_torch(idx_dev[t])
+        NB = 2
+        idx_dev = [torch.empty_like(pool[0]) for _ in range(NB)]
+        out_dev = [out, torch.empty_like(out)]
+        grad_dev = [grad, torch.empty_like(grad)]
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        in_ev = [torch.cuda.Event() for _ in range(NB)]
+        fwd_ev = [torch.cuda.Event() for _ in range(NB)]
+        d2h_ev = [torch.cuda.Event() for _ in range(NB)]
+        done_ev = [torch.cuda.Event() for _ in range(NB)]
+        issued = [False] * NB
 
-        def e2e_step():
-            idx_dev.copy_(idx_host, non_blocking=True)
+        def e2e_step(i):
+            b = i % NB
+            with torch.cuda.stream(s_in):
+                if issued[b]:
+                    s_in.wait_event(done_ev[b])          # step i-2 no longer reads these buffers
+                idx_dev[b].copy_(idx_host, non_blocking=True)
+                grad_dev[b].copy_(grad_host, non_blocking=True)
+                in_ev[b].record(s_in)
+            stream.wait_event(in_ev[b])
+            if issued[b]:
+                stream.wait_event(d2h_ev[b])             # step i-2's outputs have left out_dev[b]
+            for t in range(T):
+                ins[t].attach_torch(idx_dev[b][t])
+                outs[t].attach_torch(out_dev[b][:, t * D:(t + 1) * D])
+                outs[t].attach_torch(grad_dev[b][:, t * D:(t + 1) * D], grad=True)
             m.forward()
-            out_host.copy_(out, non_blocking=True)
-            grad.copy_(grad_host, non_blocking=True)
+            fwd_ev[b].record(stream)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(fwd_ev[b])
+                out_host.copy_(out_dev[b], non_blocking=True)
+                d2h_ev[b].record(s_out)
             m.zero_gradients()
             m.backward()
             m.update()
-            torch.cuda.synchronize()       # the host now owns this step's pooled output
+            done_ev[b].record(stream)
+            issued[b] = True
+            if i > 0:
+                d2h_ev[(i - 1) % NB].synchronize()       # the host now owns step i-1's pooled output
 
-        for _ in range(2):
-            e2e_step()
+        for i in range(NB):
+            e2e_step(i)
+        torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
-        for _ in range(args.e2e_steps):
-            e2e_step()
+        for i in range(args.e2e_steps):
+            e2e_step(NB + i)
+        s_out.synchronize()
+        stream.wait_stream(s_out)
+        stream.wait_stream(s_in)
         e.record()
         torch.cuda.synchronize()
         e2e_ms = s.elapsed_time(e) / args.e2e_steps
         line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                        "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
-                       "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps}
+                       "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
+                       "pipelining": "double-buffered: H2D of step i+1 and D2H of step i-1 overlap step i"}
         m.sync()
-        del idx_host, grad_host, out_host
+        del idx_host, grad_host, out_host, idx_dev, out_dev, grad_dev
 
     if not args.no_cpu_baseline and rank == 0 and world == 1:
         cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
