@@ -46,6 +46,10 @@ def parse_args():
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N>1: fused peer-memory exchange inside the kernels, or NCCL all-to-all")
     ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balance"])
+    ap.add_argument("--replicate", default="auto",
+                    help="N>1: keep tables with fewer rows than this on every rank (data-parallel, gradient "
+                         "all-reduce) instead of sharding them; 'auto' = batch/N (the break-even of SURVEY 7), "
+                         "'off' = shard everything as the reference's strategy files do")
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="replay the step from CUDA graphs.  auto: where the step is launch-bound -- the small "
                          "workloads on one GPU, and every sharded run; the big one-GPU steps are GPU-bound and "
@@ -531,25 +535,36 @@ def run_sharded(args, w, rank, world, local_rank):
     if args.placement == "balance":
         import dlrm_flexflow_b200 as ff
         owners = ff.balance_placement(rows, [B * L] * T, D, world, 150 << 30)
-    plan = ShardPlan(rows, D, B, world, owners=owners)
+    plan = ShardPlan(rows, D, B, world, owners=owners,
+                     replicate_below={"auto": "auto", "off": 0}.get(args.replicate, args.replicate))
     sh = ShardedEmbeddingBags(plan, rank, L, aggr, args.lr, exchange=args.exchange,
                               presort=os.environ.get("FFEMB_PRESORT", "1") == "1",
                               barrier=os.environ.get("FFEMB_BARRIER", "peer"),
                               backward_exchange=os.environ.get("FFEMB_BWD", "auto"))
     mine = plan.tables_of(rank)
+    n_mine = len(mine)
     gen = torch.Generator(device="cuda")
     gen.manual_seed(4321 + rank)
-    pool = [[workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen) for t in mine]
+    # per batch: whole-batch indices of this rank's sharded tables, then this rank's
+    # own samples' indices of the replicated tables
+    pool = [[workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen) for t in mine] +
+            [workloads.gen_indices(torch, rows[t], plan.Bs, L, args.dist, args.alpha, gen) for t in plan.replicated]
             for _ in range(args.pool)]
     sh.grad.normal_(generator=gen)
+
+    def fwd(x):
+        return sh.forward(x[:n_mine], x[n_mine:] or None)
+
+    def bwd(x):
+        sh.backward_update(x[:n_mine], x[n_mine:] or None)
 
     def step(p, ev=None):
         if ev:
             ev[0].record()
-        sh.forward(pool[p])
+        fwd(pool[p])
         if ev:
             ev[1].record()
-        sh.backward_update(pool[p])
+        bwd(pool[p])
         if ev:
             ev[2].record()
 
@@ -565,17 +580,17 @@ def run_sharded(args, w, rank, world, local_rank):
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(2):
-                sh.forward(idx_static)
-                sh.backward_update(idx_static)
+                fwd(idx_static)
+                bwd(idx_static)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         dist.barrier()
         l0 = kernels.kernel_launch_count()
         g_fwd, g_bwd = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         with torch.cuda.graph(g_fwd):
-            sh.forward(idx_static)
+            fwd(idx_static)
         with torch.cuda.graph(g_bwd):
-            sh.backward_update(idx_static)
+            bwd(idx_static)
         launches_per_step = kernels.kernel_launch_count() - l0
 
         def step(p, ev=None):      # noqa: F811
@@ -627,8 +642,8 @@ def run_sharded(args, w, rank, world, local_rank):
     peak, peak_src = measured_peaks()
     n_lookups = T * B * L
     step_bytes = n_lookups * D * 4 + 2 * U * D * 4
-    my_bytes = len(mine) * B * L * D * 4 + 2 * my_u * D * 4
-    xbytes = plan.exchange_bytes_per_rank(0)
+    my_bytes = (len(mine) * B + len(plan.replicated) * plan.Bs) * L * D * 4 + 2 * my_u * D * 4
+    xbytes = max(plan.exchange_bytes_per_rank(r) for r in range(world))
     line = {
         "metric": METRIC, "value": B / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": total_ms, "higher_is_better": True, "scaling": "strong",
@@ -642,7 +657,10 @@ def run_sharded(args, w, rank, world, local_rank):
         "phases": {"forward_and_exchange": {"ms": fwd_ms}, "exchange_sort_update": {"ms": bwd_ms}},
         "exchange": {"mode": args.exchange, "bytes_per_gpu_per_direction": xbytes,
                      "fwd_lower_bound_bus_gbs": xbytes / fwd_ms / 1e6, "nvlink_peak_gbs": 900.0,
-                     "tables_per_rank": [len(plan.tables_of(r)) for r in range(world)],
+                     "backward": sh.bwd_mode if args.exchange == "p2p" else "all_to_all",
+                     "sharded_tables_per_rank": [len(plan.tables_of(r)) for r in range(world)],
+                     "replicated_tables": len(plan.replicated), "replicate_below_rows": plan.replicate_below,
+                     "replica_allreduce_bytes": plan.replica_allreduce_bytes(),
                      "imbalance_bound": plan.imbalance_bound()},
         "clocks": clocks, "gpu_launches": int(launches),
     }
@@ -658,10 +676,10 @@ def run_sharded(args, w, rank, world, local_rank):
         def e2e_step():
             for d, h in zip(idx_dev, idx_host):
                 d.copy_(h, non_blocking=True)
-            out = sh.forward(idx_dev)
+            out = fwd(idx_dev)
             out_host.copy_(out, non_blocking=True)
             sh.grad.copy_(grad_host, non_blocking=True)
-            sh.backward_update(idx_dev)
+            bwd(idx_dev)
             torch.cuda.synchronize()
 
         for _ in range(2):

@@ -73,6 +73,7 @@ SIGNATURES = {
     "ffemb_static_scratch_bytes": (_sz, []),
     "ffemb_embed_backward_sgd_static": (_i, [_LP, _i, _i, _i, _i, _MP, _f, _vp, _vp]),
     "ffemb_uniform_init": (_i, [_vp, _i64, _i, _f, _f, _vp]),
+    "ffemb_dense_sgd": (_i, [_vp, _vp, _i64, _f, _vp]),
     "ffemb_device_malloc": (_i, [C.POINTER(C.c_void_p), _sz]),
     "ffemb_device_free": (_i, [_vp]),
     "ffemb_ipc_get_handle": (_i, [_vp, _vp]),

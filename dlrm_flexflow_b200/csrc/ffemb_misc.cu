@@ -60,3 +60,28 @@ extern "C" int ffemb_uniform_init(float *weight, int64_t count, int seed, float 
   FFEMB_LAUNCH_OK("uniform_init");
   return FFEMB_OK;
 }
+
+namespace ffemb {
+// Dense SGD for small replicated tables: the reference's sgd_update with
+// weight_decay = momentum = 0 (src/runtime/optimizer_kernel.cu:23-41),
+// W = fmaf(-lr, G, W), and G is zeroed for the next step in the same pass
+// (the reference zeroes it separately, src/runtime/model.cc:256-280).
+__global__ void __launch_bounds__(256)
+dense_sgd_kernel(float *__restrict__ w, float *__restrict__ g, int64_t count, float lr) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+    w[i] = fmaf(-lr, g[i], w[i]);
+    g[i] = 0.f;
+  }
+}
+}  // namespace ffemb
+
+extern "C" int ffemb_dense_sgd(float *weight, float *grad, int64_t count, float lr, void *stream) {
+  if (!weight || !grad || count < 0) return fail(FFEMB_ERR_INVALID_ARGUMENT, "dense_sgd: bad arguments");
+  if (count == 0) return FFEMB_OK;
+  int64_t blocks = (count + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  dense_sgd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(weight, grad, count, lr);
+  FFEMB_LAUNCH_OK("dense_sgd");
+  return FFEMB_OK;
+}

@@ -37,16 +37,33 @@ from ._lib import check, lib
 
 
 class ShardPlan(object):
-    def __init__(self, rows, dim, global_batch, world, owners=None, strategy=None):
+    """Which rank owns which table, and which small tables are replicated.
+
+    replicate_below: tables with fewer rows than this are kept on EVERY rank
+    (the reference's data-parallel embedding: replicated table, gradient
+    replicas summed, src/runtime/model.cc:697-724) instead of sharded.  A
+    replica costs a dense all-reduce of N_t*D*4 bytes per step, a shard costs
+    two exchanges of B*D*4*(N-1)/N^2 per GPU: replicate iff N_t < B/N
+    (hard part 1).  "auto" applies that rule; 0 replicates nothing.
+    owner[t] is -1 for a replicated table.
+    """
+
+    def __init__(self, rows, dim, global_batch, world, owners=None, strategy=None, replicate_below=0):
         if global_batch % world:
             raise ValueError("global batch %d is not divisible by world size %d" % (global_batch, world))
         self.rows = list(rows)
         self.T, self.D, self.B, self.N = len(rows), dim, global_batch, world
         self.Bs = global_batch // world
+        if replicate_below == "auto":
+            replicate_below = self.Bs if world > 1 else 0
+        self.replicate_below = int(replicate_below) if world > 1 else 0
+        self.replicated = [t for t in range(self.T) if self.rows[t] < self.replicate_below]
         if owners is None:
             handle = strategy.handle if strategy is not None else _lib.Handle(None)
             owners = [lib().ffemb_strategy_device_for_table(handle, t, None, world) for t in range(self.T)]
-        if len(owners) != self.T or any(not 0 <= o < world for o in owners):
+        owners = [-1 if t in self.replicated else o for t, o in enumerate(owners)]
+        if len(owners) != self.T or any(not 0 <= o < world for t, o in enumerate(owners)
+                                         if t not in self.replicated):
             raise ValueError("owners must name a rank in [0, world) for every table")
         self.owner = list(owners)
         self.local = [[t for t in range(self.T) if self.owner[t] == r] for r in range(world)]
@@ -77,9 +94,14 @@ class ShardPlan(object):
         return [len(self.local[r]) * self.B * bag for r in range(self.N)]
 
     def imbalance_bound(self):
-        """Best possible scaling efficiency from the integer table split alone."""
+        """Best possible scaling efficiency from the integer split of the sharded tables alone."""
         most = max(len(l) for l in self.local)
-        return self.T / float(self.N * most) if most else 1.0
+        sharded = self.T - len(self.replicated)
+        return sharded / float(self.N * most) if most else 1.0
+
+    def replica_allreduce_bytes(self):
+        """Dense gradient bytes all-reduced per step for the replicated tables."""
+        return sum(self.rows[t] for t in self.replicated) * self.D * 4
 
     def exchange_bytes_per_rank(self, rank):
         """Bytes that leave `rank` over NVLink per direction per step."""
@@ -183,6 +205,27 @@ class ShardedEmbeddingBags(object):
         self.workspace = kernels.alloc_workspace(max(n_lookups, 1), sum(plan.rows[t] for t in self.tables_idx) + 1, D)
         self.err = torch.zeros(1, dtype=torch.int32, device="cuda")
         self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        # Small tables kept on every rank: all replicas in one flat buffer (so one
+        # all-reduce and one dense step cover them), same seeds => identical copies.
+        self.rep_idx = list(plan.replicated)
+        self.rep_tables, self._rep_grads = [], []
+        if self.rep_idx:
+            total = sum(plan.rows[t] for t in self.rep_idx) * D
+            self._rep_W = torch.empty(total, device="cuda")
+            self._rep_G = torch.zeros(total, device="cuda")
+            pos = 0
+            for t in self.rep_idx:
+                n = plan.rows[t] * D
+                w = self._rep_W[pos:pos + n].view(plan.rows[t], D)
+                r = (1.0 / plan.rows[t]) ** 0.5
+                kernels.uniform_init(w, init_seed + t, -r, r)
+                self.rep_tables.append(w)
+                self._rep_grads.append(self._rep_G[pos:pos + n].view(plan.rows[t], D))
+                pos += n
+            self._rep_cols = [plan.global_col(t) for t in self.rep_idx]
+            self._rep_ws = kernels.alloc_workspace(len(self.rep_idx) * Bs * bag,
+                                                   sum(plan.rows[t] for t in self.rep_idx) + 1, D)
+            self._rep_stream = torch.cuda.Stream()
         self._peers = []
         self._peer_flags = None
         self._push = None
@@ -231,13 +274,15 @@ class ShardedEmbeddingBags(object):
             self._out_mat = kernels.make_matrix(([b for b in base], T * D), rows_per_part=Bs)
             self._out_cols = [plan.global_col(t) for t in self.tables_idx]
             # backward: table t's block of my gradient goes to rows [rank*Bs, ..) of owner(t)'s staging
-            items = (_lib.Push * T)()
-            for t in range(T):
+            sharded = [t for t in range(T) if plan.owner[t] >= 0]
+            items = (_lib.Push * max(len(sharded), 1))()
+            for i, t in enumerate(sharded):
                 q = plan.owner[t]
                 wq = plan.width(q)
-                items[t].dst = base[q] + (off_stage + rank * Bs * wq + plan.local_col(t)) * 4
-                items[t].dst_ld = wq
-                items[t].src_col = plan.global_col(t)
+                items[i].dst = base[q] + (off_stage + rank * Bs * wq + plan.local_col(t)) * 4
+                items[i].dst_ld = wq
+                items[i].src_col = plan.global_col(t)
+            self._n_push = len(sharded)
             if self.bwd_mode == "push":
                 self._push = items
                 self._grad_mat = kernels.make_matrix(([self._buf.ptr + off_stage * 4], max(w_me, 4)),
@@ -257,8 +302,8 @@ class ShardedEmbeddingBags(object):
             else:
                 w = w_me
                 self._fwd_send = torch.empty(N * Bs * max(w, 1), device="cuda")
-                self._fwd_recv = torch.empty(Bs * T * D, device="cuda")
-                self._bwd_send = torch.empty(Bs * T * D, device="cuda")
+                self._fwd_recv = torch.empty(Bs * sum(plan.width(r) for r in range(N)), device="cuda")
+                self._bwd_send = torch.empty(Bs * sum(plan.width(r) for r in range(N)), device="cuda")
                 self._bwd_recv = torch.empty(N * Bs * max(w, 1), device="cuda")
                 ptr = self._fwd_send.data_ptr()
                 self._out_mat = kernels.make_matrix(([ptr + q * Bs * w * 4 for q in range(N)], max(w, 4)),
@@ -316,10 +361,19 @@ class ShardedEmbeddingBags(object):
         done.record(self._side)
         return done
 
-    def forward(self, indices):
+    def _rep_lookups(self, weights, rep_indices):
+        if rep_indices is None or len(rep_indices) != len(self.rep_idx):
+            raise ValueError("expected [B/N, bag] indices of this rank's own samples for the %d replicated "
+                             "tables %s" % (len(self.rep_idx), self.rep_idx))
+        return self.K.make_lookups(weights, rep_indices, cols=self._rep_cols)
+
+    def forward(self, indices, rep_indices=None):
         plan, K, torch = self.plan, self.K, self.torch
         self._sorted_for = None
         self._mark("fwd_begin")
+        if self.rep_idx:    # replicated tables: this rank's own samples, straight into its own slice
+            K.embed_forward(self._rep_lookups(self.rep_tables, rep_indices), plan.Bs, plan.D, self.aggr,
+                            K.make_matrix(self.out), self.err)
         if self.tables:
             lk = self._lookups(indices, self._out_cols)
             done = None
@@ -340,8 +394,27 @@ class ShardedEmbeddingBags(object):
         self._mark("fwd_end")
         return self.out
 
-    def backward_update(self, indices):
+    def backward_update(self, indices, rep_indices=None):
         plan, K, torch = self.plan, self.K, self.torch
+        rep_done = None
+        if self.rep_idx:
+            # Replicas (the reference's data-parallel embedding): dense gradient of this rank's own
+            # samples (the sort/segment-reduce kernels with lr = -1 into a zeroed G), replicas summed
+            # by an all-reduce, the same dense SGD step on every rank.  On its own stream, under the
+            # exchange of the sharded tables.
+            main = torch.cuda.current_stream()
+            ready = torch.cuda.Event()
+            ready.record(main)
+            with torch.cuda.stream(self._rep_stream):
+                self._rep_stream.wait_event(ready)
+                K.embed_backward_sgd(self._rep_lookups(self._rep_grads, rep_indices), plan.Bs, plan.D, self.aggr,
+                                     K.make_matrix(self.grad), -1.0, self._rep_ws, self.err)
+                self.dist.all_reduce(self._rep_G, group=self.group)
+                check(lib().ffemb_dense_sgd(C.c_void_p(self._rep_W.data_ptr()), C.c_void_p(self._rep_G.data_ptr()),
+                                            self._rep_W.numel(), self.lr,
+                                            C.c_void_p(self._rep_stream.cuda_stream)))
+                rep_done = torch.cuda.Event()
+                rep_done.record(self._rep_stream)
         lk = self._lookups(indices, self._grad_cols) if self.tables else None
         done = None
         presorted = lk is not None and self._sorted_for == [i.data_ptr() for i in indices]
@@ -354,7 +427,7 @@ class ShardedEmbeddingBags(object):
                                         plan.backward_send_splits(self.rank), group=self.group)
         elif plan.N > 1:
             if self._push is not None:
-                check(lib().ffemb_push_columns(self._push, plan.T, plan.Bs, plan.D,
+                check(lib().ffemb_push_columns(self._push, self._n_push, plan.Bs, plan.D,
                                                C.c_void_p(self.grad.data_ptr()), self.grad.stride(0),
                                                C.c_void_p(torch.cuda.current_stream().cuda_stream)))
                 self._mark("push_done")
@@ -370,6 +443,8 @@ class ShardedEmbeddingBags(object):
                 K.embed_backward_sgd(lk, plan.B, plan.D, self.aggr, self._grad_mat, self.lr, self.workspace,
                                      self.err)
             self._sorted_for = None
+        if rep_done is not None:
+            torch.cuda.current_stream().wait_event(rep_done)
         self._mark("bwd_end")
 
     def check_errors(self):

@@ -185,6 +185,18 @@ int ffemb_embed_backward_sgd_static(const ffemb_lookup_t *lookups,
 int ffemb_uniform_init(float *weight, int64_t count, int seed, float min_val,
                        float max_val, void *stream);
 
+/* Dense SGD step W[i] = fmaf(-lr, G[i], W[i]) followed by G[i] = 0: the
+ * reference's sgd_update (src/runtime/optimizer_kernel.cu:23-41, wd = m = 0)
+ * plus its zero_gradients (src/runtime/model.cc:256-280).  Used for small
+ * tables that are replicated on every rank instead of sharded -- the
+ * reference's data-parallel embedding (replicated table, summed gradient
+ * replicas: src/runtime/model.cc:697-724, optimizer_kernel.cu:96-101): each
+ * rank builds the dense gradient of its own samples with
+ * ffemb_embed_backward_sgd(lr = -1) into a zeroed G, the replicas are summed
+ * by an all-reduce, and every rank applies the same dense step. */
+int ffemb_dense_sgd(float *weight, float *grad, int64_t count, float lr,
+                    void *stream);
+
 /* Peer-memory plumbing of the table-wise sharded path (one process per GPU).
  * Stands in for what Legion DMA does for the reference: embedding outputs and
  * their gradients cross GPUs through zero-copy host memory

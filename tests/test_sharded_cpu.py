@@ -36,6 +36,19 @@ def test_plan_round_robin_and_layout():
         ShardPlan([10] * 4, 16, 32, 4, owners=[0, 1, 2, 7])
 
 
+def test_plan_replicates_small_tables():
+    from dlrm_flexflow_b200.workloads import TERABYTE_ROWS
+    plan = ShardPlan(TERABYTE_ROWS, 128, 65536, 8, replicate_below="auto")     # rule: N_t < B/N = 8192
+    assert plan.replicate_below == 8192
+    assert plan.replicated == [t for t, n in enumerate(TERABYTE_ROWS) if n < 8192] and len(plan.replicated) == 13
+    assert all(plan.owner[t] == -1 for t in plan.replicated)
+    assert all(plan.owner[t] == t % 8 for t in range(26) if t not in plan.replicated)
+    assert max(len(plan.tables_of(r)) for r in range(8)) == 2           # exchange volume halves (4 -> 2 tables)
+    assert plan.replica_allreduce_bytes() == sum(TERABYTE_ROWS[t] for t in plan.replicated) * 128 * 4 < 11e6
+    assert ShardPlan(TERABYTE_ROWS, 128, 65536, 1, replicate_below="auto").replicated == []   # one GPU: nothing
+    assert ShardPlan(TERABYTE_ROWS, 128, 65536, 8).replicated == []                           # default: off
+
+
 def test_plan_follows_a_strategy_file():
     s = ff.Strategy.dlrm_simple(8, 16)           # the reference's 16embs_8gpus fixture
     plan = ShardPlan([100] * 16, 64, 1024, 8, strategy=s)
