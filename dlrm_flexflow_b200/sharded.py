@@ -244,6 +244,7 @@ class ShardedEmbeddingBags(object):
         # NVLink-bound gradient push when there are several.
         self._presort = presort
         self._sorted_for = None
+        self._rep_sorted_for = None
         self._side = torch.cuda.Stream(priority=-1) if presort else None
         self.grad = None
         w_me = plan.width(rank)
@@ -371,9 +372,24 @@ class ShardedEmbeddingBags(object):
         plan, K, torch = self.plan, self.K, self.torch
         self._sorted_for = None
         self._mark("fwd_begin")
+        self._rep_sorted_for = None
         if self.rep_idx:    # replicated tables: this rank's own samples, straight into its own slice
+            if self._presort:
+                # their backward is a chain of small latency-bound kernels that would otherwise end up
+                # on the critical path of backward_update: sort the keys now, under the gather
+                main = torch.cuda.current_stream()
+                ready = torch.cuda.Event()
+                ready.record(main)
+                self._rep_stream.wait_event(ready)
+                K.embed_backward_sort(self._rep_lookups(self._rep_grads, rep_indices), plan.Bs, plan.D,
+                                      self._rep_ws, self.err, stream=self._rep_stream)
+                rep_sorted = torch.cuda.Event()
+                rep_sorted.record(self._rep_stream)
             K.embed_forward(self._rep_lookups(self.rep_tables, rep_indices), plan.Bs, plan.D, self.aggr,
                             K.make_matrix(self.out), self.err)
+            if self._presort:
+                main.wait_event(rep_sorted)      # join: one timeline for callers and graph capture
+                self._rep_sorted_for = [i.data_ptr() for i in rep_indices]
         if self.tables:
             lk = self._lookups(indices, self._out_cols)
             done = None
@@ -407,8 +423,14 @@ class ShardedEmbeddingBags(object):
             ready.record(main)
             with torch.cuda.stream(self._rep_stream):
                 self._rep_stream.wait_event(ready)
-                K.embed_backward_sgd(self._rep_lookups(self._rep_grads, rep_indices), plan.Bs, plan.D, self.aggr,
-                                     K.make_matrix(self.grad), -1.0, self._rep_ws, self.err)
+                rlk = self._rep_lookups(self._rep_grads, rep_indices)
+                if self._rep_sorted_for == [i.data_ptr() for i in rep_indices]:     # forward() sorted these
+                    K.embed_sgd_update(rlk, plan.Bs, plan.D, self.aggr, K.make_matrix(self.grad), -1.0,
+                                       self._rep_ws, stream=self._rep_stream)
+                else:
+                    K.embed_backward_sgd(rlk, plan.Bs, plan.D, self.aggr, K.make_matrix(self.grad), -1.0,
+                                         self._rep_ws, self.err, stream=self._rep_stream)
+                self._rep_sorted_for = None
                 self.dist.all_reduce(self._rep_G, group=self.group)
                 check(lib().ffemb_dense_sgd(C.c_void_p(self._rep_W.data_ptr()), C.c_void_p(self._rep_G.data_ptr()),
                                             self._rep_W.numel(), self.lr,
