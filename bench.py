@@ -547,9 +547,24 @@ def run_sharded(args, w, rank, world, local_rank):
     gen.manual_seed(4321 + rank)
     # per batch: whole-batch indices of this rank's sharded tables, then this rank's
     # own samples' indices of the replicated tables
-    pool = [[workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen) for t in mine] +
-            [workloads.gen_indices(torch, rows[t], plan.Bs, L, args.dist, args.alpha, gen) for t in plan.replicated]
-            for _ in range(args.pool)]
+    # (each batch lives in ONE flat buffer so that staging it is a single copy)
+    sizes = [B * L] * n_mine + [plan.Bs * L] * len(plan.replicated)
+    shapes = [(B, L)] * n_mine + [(plan.Bs, L)] * len(plan.replicated)
+
+    def views(flat):
+        out, pos = [], 0
+        for n, shp in zip(sizes, shapes):
+            out.append(flat[pos:pos + n].view(shp))
+            pos += n
+        return out
+
+    flats = []
+    for _ in range(args.pool):
+        flat = torch.empty(max(sum(sizes), 1), dtype=torch.int64, device="cuda")
+        for v, t in zip(views(flat), list(mine) + list(plan.replicated)):
+            v.copy_(workloads.gen_indices(torch, rows[t], v.shape[0], L, args.dist, args.alpha, gen))
+        flats.append(flat)
+    pool = [views(f) for f in flats]
     sh.grad.normal_(generator=gen)
 
     def fwd(x):
@@ -573,9 +588,9 @@ def run_sharded(args, w, rank, world, local_rank):
         # forward (+ its exchange and barrier) and backward (+ barriers) as two
         # CUDA graphs over fixed index buffers; the peer barrier keeps its count
         # on the device, so replays stay in step across ranks.
-        idx_static = [torch.empty_like(x) for x in pool[0]]
-        for d, x in zip(idx_static, pool[0]):
-            d.copy_(x)
+        flat_static = torch.empty_like(flats[0])
+        flat_static.copy_(flats[0])
+        idx_static = views(flat_static)
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -596,8 +611,7 @@ def run_sharded(args, w, rank, world, local_rank):
         def step(p, ev=None):      # noqa: F811
             if ev:
                 ev[0].record()
-            for d, x in zip(idx_static, pool[p]):
-                d.copy_(x)
+            flat_static.copy_(flats[p])
             g_fwd.replay()
             if ev:
                 ev[1].record()
@@ -667,15 +681,15 @@ def run_sharded(args, w, rank, world, local_rank):
     line["config"]["placement"] = args.placement
     if not args.no_e2e:
         Bs = plan.Bs
-        idx_host = [x.cpu().pin_memory() for x in pool[0]]
-        idx_dev = [torch.empty_like(x) for x in pool[0]]
+        idx_host = flats[0].cpu().pin_memory()
+        flat_dev = torch.empty_like(flats[0])
+        idx_dev = views(flat_dev)
         grad_host = torch.empty((Bs, T * D), pin_memory=True)
         grad_host.copy_(sh.grad)
         out_host = torch.empty((Bs, T * D), pin_memory=True)
 
         def e2e_step():
-            for d, h in zip(idx_dev, idx_host):
-                d.copy_(h, non_blocking=True)
+            flat_dev.copy_(idx_host, non_blocking=True)
             out = fwd(idx_dev)
             out_host.copy_(out, non_blocking=True)
             sh.grad.copy_(grad_host, non_blocking=True)
@@ -695,7 +709,7 @@ def run_sharded(args, w, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
         line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
-                       "h2d_bytes_per_step": sum(x.numel() for x in idx_host) * 8 + grad_host.numel() * 4,
+                       "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
                        "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
                        "note": "bytes are per rank; every rank copies its own slice"}
     sh.close()
