@@ -200,6 +200,24 @@ def test_step_with_duplicates_within_tolerance(K, oracle, D, N, L, aggr):
         np.testing.assert_allclose(got[t], want[t], **TOL)
 
 
+@pytest.mark.parametrize("D,L,aggr", [(128, 1, SUM), (64, 3, AVG), (16, 1, SUM), (20, 1, SUM)])
+def test_step_very_long_runs_cross_many_blocks(K, oracle, D, L, aggr):
+    """Two-row tables: each row collects ~20 000 lookups, i.e. a run that spans far more than 32 level-1
+    blocks, so the cross-block chain is summed by the block-level kernel (reduce_l3), as for the 3- and
+    4-row tables of the MLPerf-Terabyte shape."""
+    rng = np.random.default_rng(D * 10 + L)
+    T, B = 2, 40001
+    Ws = [rng.normal(size=(2, D)).astype(np.float32) for _ in range(T)]
+    idxs = [rng.integers(0, 2, size=(B, L)) for _ in range(T)]
+    g = (0.1 * rng.normal(size=(B, T * D))).astype(np.float32)
+    got, err = run_step(K, Ws, idxs, g, aggr, 0.01)
+    want = oracle_step(oracle, Ws, idxs, g, aggr, 0.01)
+    assert err == 0
+    for t in range(T):
+        assert not np.array_equal(got[t], Ws[t])
+        np.testing.assert_allclose(got[t], want[t], **TOL)
+
+
 def test_step_short_runs_inside_one_chunk_are_bit_exact(K, oracle):
     """Each touched row has exactly 4 lookups, and runs are aligned so none
     crosses a 32-position chunk: sequential sum == CPU order, bit for bit."""
