@@ -382,16 +382,27 @@ extern "C" int ffemb_model_compile(ffemb_model_t h) {
   Model *m = M(h);
   if (!m) return fail(FFEMB_ERR_INVALID_ARGUMENT, "compile: NULL model");
   if (m->compiled) return fail(FFEMB_ERR_INVALID_ARGUMENT, "compile: model is already compiled");
+  if (!m->strategy.impl && !m->cfg.strategy_file.empty()) {
+    m->strategy = ffemb_strategy_create();
+    m->own_strategy = true;
+    if (int rc = ffemb_strategy_load_file(m->strategy, m->cfg.strategy_file.c_str())) return rc;
+  }
+  // A strategy may place an embedding on a CPU (the reference's "hetero"
+  // generator, src/runtime/dlrm_strategy_hetero.cc:27-36, whose CPU tasks are
+  // not even registered in the reference build).  There is no CPU
+  // path here: refuse it rather than run it somewhere else silently.
+  for (auto &op : m->ops) {
+    int i = ffemb_strategy_find(m->strategy, ("embedding" + std::to_string(op->index)).c_str());
+    if (i < 0) i = ffemb_strategy_find(m->strategy, op->name.c_str());
+    if (i >= 0 && ffemb_strategy_op_device_type(m->strategy, i) == FFEMB_DEVICE_CPU)
+      return fail(FFEMB_ERR_UNSUPPORTED, "compile: the strategy places " + op->name +
+                                             " on a CPU; this library has no CPU path");
+  }
   if (m->cfg.device >= 0) {
     FFEMB_CUDA_OK(cudaSetDevice(m->cfg.device));
     m->device = m->cfg.device;
   } else {
     FFEMB_CUDA_OK(cudaGetDevice(&m->device));
-  }
-  if (!m->strategy.impl && !m->cfg.strategy_file.empty()) {
-    m->strategy = ffemb_strategy_create();
-    m->own_strategy = true;
-    if (int rc = ffemb_strategy_load_file(m->strategy, m->cfg.strategy_file.c_str())) return rc;
   }
   // placement: table i -> rank (FFMapper::slice_task, mapper.cc:33-97)
   int64_t lookups = 0, entries = 0, sum_d = 0;

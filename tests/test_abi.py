@@ -227,6 +227,20 @@ def test_no_cpu_fallback_without_gpu():
         kernels.make_lookups([torch.zeros(4, 4)], [torch.zeros(2, 1, dtype=torch.int64)])
 
 
+def test_cpu_placement_is_refused_not_emulated():
+    """The reference's hetero strategy (dlrm_strategy_hetero.cc:27-36) puts embeddings on CPUs; this
+    library has no CPU path and says so at compile, before touching any device."""
+    cfg, m = _model(8)
+    t = m.create_tensor([8, 1], ff.DataType.DT_INT64)
+    m.embedding(t, 10, 4, ff.AggrMode.AGGR_MODE_SUM)
+    s = ff.Strategy()
+    s.add_op("embedding0", 1, [1, 1], [0])        # device_type CPU
+    m.set_strategy(s)
+    with pytest.raises(ff.FFEmbError) as e:
+        m.compile(ff.SGDOptimizer(m, 0.01))
+    assert e.value.status == _lib.FFEMB_ERR_UNSUPPORTED and "CPU" in str(e.value)
+
+
 def test_product_never_imports_the_oracle():
     pkg = os.path.join(ROOT, "dlrm_flexflow_b200")
     for dirpath, _, files in os.walk(pkg):
