@@ -33,7 +33,11 @@ constexpr int kBwdThreads = 256;
 #define FFEMB_BU 8
 #endif
 constexpr int kBU = FFEMB_BU;     // positions whose rows are in flight together
-constexpr int kShortChain = 32;   // reduce_l2 sums chains up to this many partials itself
+// reduce_l2 sums chains up to this many partials itself (one sub-warp, 8 loads
+// in flight); longer ones go to reduce_l3, where a whole block shares the chain.
+// Measured on C3 (whose 3-row table makes chains of 85 at D = 128): 32 -> update
+// phase 0.306 ms, 128 -> 0.313 ms, so the second kernel pays for itself early.
+constexpr int kShortChain = 32;
 #ifndef FFEMB_L1_MINBLOCKS
 #define FFEMB_L1_MINBLOCKS 2
 #endif

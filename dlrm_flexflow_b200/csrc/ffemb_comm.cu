@@ -4,10 +4,12 @@
 // implicitly: Embedding maps its output to zero-copy host memory
 // (src/ops/embedding.cu:280-284,343-347) and Concat re-partitions it
 // (src/ops/concat.cu:85-93), Legion DMA doing the copies through the host.
-// Here every rank (one process per GPU) exposes its [B/N][T*D] output and
-// gradient matrices to its peers by CUDA IPC; the forward kernel then stores
-// pooled rows straight into the consuming rank's matrix over NVLink and the
-// update kernel loads gradient rows straight from the producing rank's.
+// Here every rank (one process per GPU) exposes its [B/N][T*D] output matrix
+// and its gradient staging to its peers by CUDA IPC; the forward kernel then
+// stores pooled rows straight into the consuming rank's matrix over NVLink,
+// push_columns_kernel stores gradient blocks straight into the owning rank's
+// staging (or, "pull", the update kernel loads gradient rows from the
+// producing rank's matrix), and peer_barrier_kernel orders the ranks.
 #include <string.h>
 
 #include "ffemb_common.cuh"
@@ -49,7 +51,7 @@ extern "C" int ffemb_ipc_close_handle(void *device_ptr) {
 
 // ---------------------------------------------------------------------------
 // Stream-ordered barrier among the ranks of one box, over peer memory.
-// Every rank owns FFEMB_BARRIER_WORDS 32-bit words, zeroed once: word q < world
+// Every rank owns 32 32-bit words, zeroed once: word q < world
 // is the flag written by rank q, word 16 is this rank's barrier count.  The
 // kernel bumps the count to `epoch` (kept on the device, so a captured launch
 // can be replayed), thread q stores `epoch` into peer q's flag[rank] (an

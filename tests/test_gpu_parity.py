@@ -200,16 +200,18 @@ def test_step_with_duplicates_within_tolerance(K, oracle, D, N, L, aggr):
         np.testing.assert_allclose(got[t], want[t], **TOL)
 
 
-@pytest.mark.parametrize("D,L,aggr", [(128, 1, SUM), (64, 3, AVG), (16, 1, SUM), (20, 1, SUM)])
-def test_step_very_long_runs_cross_many_blocks(K, oracle, D, L, aggr):
-    """Two-row tables: each row collects ~20 000 lookups, i.e. a run that spans far more than 32 level-1
-    blocks, so the cross-block chain is summed by the block-level kernel (reduce_l3), as for the 3- and
-    4-row tables of the MLPerf-Terabyte shape."""
+@pytest.mark.parametrize("D,L,aggr,B", [(128, 1, SUM, 40001), (64, 3, AVG, 40001), (16, 1, SUM, 40001),
+                                        (20, 1, SUM, 40001), (128, 1, SUM, 160001), (64, 4, AVG, 100001)])
+def test_step_very_long_runs_cross_many_blocks(K, oracle, D, L, aggr, B):
+    """Two-row tables: each row collects tens of thousands of lookups, i.e. a run that spans many level-1
+    blocks (like the 3- and 4-row tables of the MLPerf-Terabyte shape).  Chains of more than 32 partials
+    go to the block-level kernel reduce_l3: ~80 partials in the 40001-bag cases at D = 128, 300-400 in
+    the large ones; the D = 16 case (2048-position blocks) stays a short chain for reduce_l2."""
     rng = np.random.default_rng(D * 10 + L)
-    T, B = 2, 40001
+    T = 2
     Ws = [rng.normal(size=(2, D)).astype(np.float32) for _ in range(T)]
     idxs = [rng.integers(0, 2, size=(B, L)) for _ in range(T)]
-    g = (0.1 * rng.normal(size=(B, T * D))).astype(np.float32)
+    g = (0.05 * rng.normal(size=(B, T * D))).astype(np.float32)
     got, err = run_step(K, Ws, idxs, g, aggr, 0.01)
     want = oracle_step(oracle, Ws, idxs, g, aggr, 0.01)
     assert err == 0
