@@ -70,6 +70,8 @@ SIGNATURES = {
     "ffemb_embed_backward_sgd": (_i, [_LP, _i, _i, _i, _i, _MP, _f, _vp, _sz, _vp, _vp]),
     "ffemb_embed_backward_sort": (_i, [_LP, _i, _i, _i, _vp, _sz, _vp, _vp]),
     "ffemb_embed_sgd_update": (_i, [_LP, _i, _i, _i, _i, _MP, _f, _vp, _sz, _vp]),
+    "ffemb_set_sort_impl": (_i, [_i]),
+    "ffemb_get_sort_impl": (_i, []),
     "ffemb_static_scratch_bytes": (_sz, []),
     "ffemb_embed_backward_sgd_static": (_i, [_LP, _i, _i, _i, _i, _MP, _f, _vp, _vp]),
     "ffemb_uniform_init": (_i, [_vp, _i64, _i, _f, _f, _vp]),

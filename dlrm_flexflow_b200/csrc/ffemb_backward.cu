@@ -24,8 +24,12 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include "ffemb_common.cuh"
+#include "ffemb_sort.cuh"
 
 namespace ffemb {
+
+// 0: CUB DeviceRadixSort (library), 1: the segmented per-table sort of ffemb_sort.cuh
+std::atomic<int> g_sort_impl{0};
 
 constexpr int kChunk = 32;  // sorted positions per sub-warp in reduce_l1
 constexpr int kBwdThreads = 256;
@@ -583,6 +587,7 @@ static Workspace carve(void *base, int64_t n, int64_t total_entries, int D) {
   w.vals_a = (uint32_t *)take(n * 4);
   w.vals_b = (uint32_t *)take(n * 4);
   w.sort_tmp_bytes = sort_tmp_bytes(n, wide);
+  if (!wide && own_sort_hist_bytes(n) > w.sort_tmp_bytes) w.sort_tmp_bytes = own_sort_hist_bytes(n);
   w.sort_tmp = take(w.sort_tmp_bytes);
   w.part0 = (float *)take((size_t)blocks * D * 4);
   w.part1 = (float *)take((size_t)blocks * D * 4);
@@ -632,6 +637,9 @@ static Group group_of(const ffemb_lookup_t *lookups, int T) {
 template <typename KeyT>
 static int sort_group(const ffemb_lookup_t *lookups, int T, int batch, const Workspace &w,
                       const Group &g, int *err, cudaStream_t s) {
+  if (sizeof(KeyT) == 4 && g_sort_impl.load(std::memory_order_relaxed) == 1)
+    return own_sort_group(lookups, T, batch, (uint32_t *)w.keys_a, (uint32_t *)w.keys_b, w.vals_a,
+                          w.vals_b, (uint32_t *)w.sort_tmp, err, s);
   KeyParams kp;
   int64_t rows = 0, pos = 0, max_n = 0;
   bool any_csr = false;
@@ -745,6 +753,13 @@ static int backward_impl(int phases, const ffemb_lookup_t *lookups, int num_tabl
 }  // namespace ffemb
 
 using namespace ffemb;
+
+extern "C" int ffemb_set_sort_impl(int impl) {
+  if (impl != 0 && impl != 1) return fail(FFEMB_ERR_INVALID_ARGUMENT, "set_sort_impl: 0 (library) or 1 (own)");
+  g_sort_impl.store(impl);
+  return FFEMB_OK;
+}
+extern "C" int ffemb_get_sort_impl(void) { return g_sort_impl.load(); }
 
 extern "C" size_t ffemb_embed_backward_workspace_bytes(int64_t total_indices,
                                                        int64_t total_entries, int out_dim) {

@@ -156,5 +156,14 @@ def uniform_init(weight, seed, min_val, max_val, stream=None):
                                         min_val, max_val, _stream_ptr(stream)))
 
 
+def set_sort_impl(impl):
+    """0: CUDA toolkit DeviceRadixSort; 1: the library's own segmented per-table sort."""
+    check(_lib.lib().ffemb_set_sort_impl(int(impl)))
+
+
+def get_sort_impl():
+    return _lib.lib().ffemb_get_sort_impl()
+
+
 def kernel_launch_count():
     return _lib.lib().ffemb_kernel_launch_count()

@@ -138,6 +138,15 @@ int ffemb_embed_backward_sgd(const ffemb_lookup_t *lookups, int num_tables,
                              void *workspace, size_t workspace_bytes,
                              int *err_flag, void *stream);
 
+/* Which key sort the backward uses (process-wide).  0: the CUDA toolkit's
+ * DeviceRadixSort over the global (table,row) keys; 1: this library's own
+ * segmented sort (csrc/ffemb_sort.cuh), which sorts every table's segment by
+ * row number with only as many passes as that table's size needs.  Both are
+ * stable, so they produce the same order and bit-identical results.  Launch
+ * groups whose tables hold 2^32-1 rows or more always use 0. */
+int ffemb_set_sort_impl(int impl);
+int ffemb_get_sort_impl(void);
+
 /* The two halves of ffemb_embed_backward_sgd, for callers that keep the
  * reference's backward() / update() split: `backward_sort` leaves the sorted
  * sparse gradient description in `workspace`; `sgd_update` consumes it.

@@ -1,0 +1,86 @@
+#!/usr/bin/env python
+"""Development check of the library's own key sort (ffemb_sort.cuh) against the
+toolkit sort: both are stable, so backward + SGD must give bit-identical tables.
+Also times the sort phase alone on the C3 shape.  Run on a GPU box."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dlrm_flexflow_b200 import kernels as K, workloads  # noqa: E402
+
+
+def step(impl, Ws, idxs, g, aggr, offsets=None, B=None):
+    K.set_sort_impl(impl)
+    D = Ws[0].shape[1]
+    B = B if B is not None else idxs[0].shape[0]
+    dW = [w.clone() for w in Ws]
+    n = sum(i.numel() for i in idxs)
+    ws = K.alloc_workspace(n, sum(w.shape[0] for w in Ws), D)
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    K.embed_backward_sgd(K.make_lookups(dW, idxs, offsets), B, D, aggr, g, 0.05, ws, err)
+    torch.cuda.synchronize()
+    return dW, int(err.item())
+
+
+def main():
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(0)
+    ok = True
+    cases = [
+        ([3, 1, 700, 5000, 100000, 70000, 2, 513, 511, 512], 64, 4096, 1, 21),
+        ([1000000, 17, 40000000 // 8], 128, 8192, 1, 21),
+        ([300, 65536, 9], 32, 1000, 5, 22),
+        ([2000] * 70, 16, 333, 2, 21),
+    ]
+    for rows, D, B, L, aggr in cases:
+        Ws = [torch.randn(n, D, device="cuda", generator=gen) for n in rows]
+        idxs = [torch.randint(0, n, (B, L), device="cuda", generator=gen) for n in rows]
+        idxs[0][0, 0] = rows[0]          # one out-of-range index
+        idxs[-1][B - 1, L - 1] = -5
+        g = torch.randn(B, len(rows) * D, device="cuda", generator=gen)
+        a, ea = step(0, Ws, idxs, g, aggr)
+        b, eb = step(1, Ws, idxs, g, aggr)
+        same = all(torch.equal(x, y) for x, y in zip(a, b)) and ea == eb == 3
+        changed = any(not torch.equal(x, w) for x, w in zip(a, Ws))
+        print("case rows=%s.. D=%d B=%d L=%d: %s" % (rows[:4], D, B, L, "ok" if same and changed else "MISMATCH"))
+        ok = ok and same and changed
+    # ragged bags
+    B, D, N = 777, 64, 5000
+    lengths = torch.randint(0, 9, (B,), device="cuda", generator=gen)
+    off = torch.cat([torch.zeros(1, dtype=torch.int64, device="cuda"), lengths.cumsum(0)])
+    idx = torch.randint(0, N, (int(off[-1].item()),), device="cuda", generator=gen)
+    W = torch.randn(N, D, device="cuda", generator=gen)
+    g = torch.randn(B, D, device="cuda", generator=gen)
+    a, _ = step(0, [W], [idx], g, 22, offsets=[off], B=B)
+    b, _ = step(1, [W], [idx], g, 22, offsets=[off], B=B)
+    print("ragged:", "ok" if torch.equal(a[0], b[0]) else "MISMATCH")
+    ok = ok and torch.equal(a[0], b[0])
+    # timing of the sort phase on C3
+    w = workloads.WORKLOADS["C3"]
+    rows, D, B = w["rows"], 4, w["batch"]            # D irrelevant for the sort
+    Ws = [torch.zeros(n, D, device="cuda") for n in rows]
+    idxs = [workloads.gen_indices(torch, n, B, 1, "uniform", 0.0, gen) for n in rows]
+    ws = K.alloc_workspace(len(rows) * B, sum(rows), D)
+    lk = K.make_lookups(Ws, idxs)
+    for impl in (0, 1):
+        K.set_sort_impl(impl)
+        for _ in range(3):
+            K.embed_backward_sort(lk, B, D, ws)
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(50):
+            K.embed_backward_sort(lk, B, D, ws)
+        e.record()
+        torch.cuda.synchronize()
+        print("C3 sort phase, impl %d: %.1f us" % (impl, s.elapsed_time(e) / 50 * 1e3))
+    K.set_sort_impl(0)
+    print("ALL OK" if ok else "FAILED")
+    return 0 if ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
