@@ -13,7 +13,7 @@
 //
 // Per pass three small kernels over the tables still active:
 //   rs_hist     per 2048-key tile: digit histogram in shared memory
-//   rs_scan     per table: exclusive scan of its [digit][tile] counts
+//   rs_scan     per table: exclusive scan of its counts in digit-major order
 //   rs_scatter  per tile: stable rank of every key among equal digits
 //               (__match_any_sync inside the warp, per-warp counters across
 //               rounds, prefix over the 8 warps), then scatter.
@@ -134,33 +134,45 @@ __global__ void __launch_bounds__(kSortThreads) rs_hist_kernel(const __grid_cons
   }
   __syncthreads();
   for (int d = threadIdx.x; d < radix; d += kSortThreads)
-    p.hist[tb.hist_base + (uint32_t)d * tb.ntiles + tile] = h[d];
+    p.hist[tb.hist_base + tile * (uint32_t)radix + d] = h[d];
 }
 
-// one block per table: exclusive scan of its histogram in [digit][tile] order
+// One block per table.  The histogram is stored [tile][digit] (coalesced for
+// every kernel); the exclusive scan runs in digit-major order -- all tiles of
+// digit 0, then of digit 1, ... -- which is the order of the sorted segment.
+// Thread tid owns digits tid, tid+256, ...: it totals a digit over the tiles,
+// the block scans the totals, then the thread hands each tile its offset.
 __global__ void __launch_bounds__(kSortThreads) rs_scan_kernel(const __grid_constant__ SortParams p) {
   __shared__ uint32_t part[kSortThreads];
   const SortTable &tb = p.t[blockIdx.x];
-  const uint32_t E = tb.ntiles << p.radix_bits;
+  const uint32_t radix = 1u << p.radix_bits;
   uint32_t *h = p.hist + tb.hist_base;
-  const uint32_t per = (E + kSortThreads - 1) / kSortThreads;
-  const uint32_t b = threadIdx.x * per;
-  const uint32_t e = b + per < E ? b + per : E;
-  uint32_t s = 0;
-  for (uint32_t i = b; i < e; ++i) s += h[i];
-  part[threadIdx.x] = s;
-  __syncthreads();
-  for (int off = 1; off < kSortThreads; off <<= 1) {
-    const uint32_t v = (int)threadIdx.x >= off ? part[threadIdx.x - off] : 0u;
+  uint32_t carry = 0;  // keys with a digit below the current block of 256 digits
+  for (uint32_t d0 = 0; d0 < radix; d0 += kSortThreads) {
+    const uint32_t d = d0 + threadIdx.x;
+    uint32_t tot = 0;
+    if (d < radix) {
+#pragma unroll 8
+      for (uint32_t tile = 0; tile < tb.ntiles; ++tile) tot += h[tile * radix + d];
+    }
+    part[threadIdx.x] = tot;
     __syncthreads();
-    part[threadIdx.x] += v;
-    __syncthreads();
-  }
-  uint32_t run = part[threadIdx.x] - s;  // exclusive prefix of this thread's range
-  for (uint32_t i = b; i < e; ++i) {
-    const uint32_t v = h[i];
-    h[i] = run;
-    run += v;
+    for (int off = 1; off < kSortThreads; off <<= 1) {
+      const uint32_t v = (int)threadIdx.x >= off ? part[threadIdx.x - off] : 0u;
+      __syncthreads();
+      part[threadIdx.x] += v;
+      __syncthreads();
+    }
+    uint32_t run = carry + part[threadIdx.x] - tot;  // exclusive over digits
+    carry += part[kSortThreads - 1];
+    if (d < radix) {
+      for (uint32_t tile = 0; tile < tb.ntiles; ++tile) {
+        const uint32_t v = h[tile * radix + d];
+        h[tile * radix + d] = run;
+        run += v;
+      }
+    }
+    __syncthreads();  // part[] is reused by the next block of digits
   }
 }
 
@@ -173,7 +185,7 @@ __global__ void __launch_bounds__(kSortThreads) rs_scatter_kernel(const __grid_c
   const uint32_t tile = blockIdx.x - tb.tile_base;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int d = threadIdx.x; d < radix; d += kSortThreads) {
-    base[d] = p.hist[tb.hist_base + (uint32_t)d * tb.ntiles + tile];
+    base[d] = p.hist[tb.hist_base + tile * (uint32_t)radix + d];
 #pragma unroll
     for (int ww = 0; ww < kSortThreads / 32; ++ww) cnt[ww][d] = 0;
   }

@@ -72,7 +72,7 @@ def main():
         torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
-        for _ in range(50):
+        for _ in range(30):
             K.embed_backward_sort(lk, B, D, ws)
         e.record()
         torch.cuda.synchronize()
