@@ -29,7 +29,10 @@
 namespace ffemb {
 
 // 0: CUB DeviceRadixSort (library), 1: the segmented per-table sort of ffemb_sort.cuh
-std::atomic<int> g_sort_impl{0};
+#ifndef FFEMB_DEFAULT_SORT
+#define FFEMB_DEFAULT_SORT 0
+#endif
+std::atomic<int> g_sort_impl{FFEMB_DEFAULT_SORT};
 
 constexpr int kChunk = 32;  // sorted positions per sub-warp in reduce_l1
 constexpr int kBwdThreads = 256;

@@ -17,8 +17,9 @@ def K():
     if not torch.cuda.is_available():
         pytest.fail("needs a CUDA device")
     from dlrm_flexflow_b200 import kernels
+    default = kernels.get_sort_impl()
     yield kernels
-    kernels.set_sort_impl(0)
+    kernels.set_sort_impl(default)
 
 
 def _step(K, impl, Ws, idxs, g, aggr, B, offsets=None):
