@@ -449,74 +449,76 @@ def run_ours(args, w):
     # step i+1 and the D2H of step i-1 (PCIe is full duplex); the host picks up
     # the result of step i-1 before it issues step i+1.
     if not args.no_e2e:
-        m.set_stream(stream.cuda_stream)
-        idx_host = pool[0].cpu().pin_memory()
-        grad_host = torch.empty((B, T * D), pin_memory=True)
-        grad_host.copy_(grad)
-        out_host = torch.empty((B, T * D), pin_memory=True)
-        NB = 2
-        idx_dev = [torch.empty_like(pool[0]) for _ in range(NB)]
-        out_dev = [out, torch.empty_like(out)]
-        grad_dev = [grad, torch.empty_like(grad)]
-        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-        in_ev = [torch.cuda.Event() for _ in range(NB)]
-        fwd_ev = [torch.cuda.Event() for _ in range(NB)]
-        d2h_ev = [torch.cuda.Event() for _ in range(NB)]
-        done_ev = [torch.cuda.Event() for _ in range(NB)]
-        issued = [False] * NB
+        with _Guard(line, "e2e"):
+            m.set_stream(stream.cuda_stream)
+            idx_host = pool[0].cpu().pin_memory()
+            grad_host = torch.empty((B, T * D), pin_memory=True)
+            grad_host.copy_(grad)
+            out_host = torch.empty((B, T * D), pin_memory=True)
+            NB = 2
+            idx_dev = [torch.empty_like(pool[0]) for _ in range(NB)]
+            out_dev = [out, torch.empty_like(out)]
+            grad_dev = [grad, torch.empty_like(grad)]
+            s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+            in_ev = [torch.cuda.Event() for _ in range(NB)]
+            fwd_ev = [torch.cuda.Event() for _ in range(NB)]
+            d2h_ev = [torch.cuda.Event() for _ in range(NB)]
+            done_ev = [torch.cuda.Event() for _ in range(NB)]
+            issued = [False] * NB
 
-        def e2e_step(i):
-            b = i % NB
-            with torch.cuda.stream(s_in):
+            def e2e_step(i):
+                b = i % NB
+                with torch.cuda.stream(s_in):
+                    if issued[b]:
+                        s_in.wait_event(done_ev[b])          # step i-2 no longer reads these buffers
+                    idx_dev[b].copy_(idx_host, non_blocking=True)
+                    grad_dev[b].copy_(grad_host, non_blocking=True)
+                    in_ev[b].record(s_in)
+                stream.wait_event(in_ev[b])
                 if issued[b]:
-                    s_in.wait_event(done_ev[b])          # step i-2 no longer reads these buffers
-                idx_dev[b].copy_(idx_host, non_blocking=True)
-                grad_dev[b].copy_(grad_host, non_blocking=True)
-                in_ev[b].record(s_in)
-            stream.wait_event(in_ev[b])
-            if issued[b]:
-                stream.wait_event(d2h_ev[b])             # step i-2's outputs have left out_dev[b]
-            for t in range(T):
-                ins[t].attach_torch(idx_dev[b][t])
-                outs[t].attach_torch(out_dev[b][:, t * D:(t + 1) * D])
-                outs[t].attach_torch(grad_dev[b][:, t * D:(t + 1) * D], grad=True)
-            m.forward()
-            fwd_ev[b].record(stream)
-            with torch.cuda.stream(s_out):
-                s_out.wait_event(fwd_ev[b])
-                out_host.copy_(out_dev[b], non_blocking=True)
-                d2h_ev[b].record(s_out)
-            m.zero_gradients()
-            m.backward()
-            m.update()
-            done_ev[b].record(stream)
-            issued[b] = True
-            if i > 0:
-                d2h_ev[(i - 1) % NB].synchronize()       # the host now owns step i-1's pooled output
+                    stream.wait_event(d2h_ev[b])             # step i-2's outputs have left out_dev[b]
+                for t in range(T):
+                    ins[t].attach_torch(idx_dev[b][t])
+                    outs[t].attach_torch(out_dev[b][:, t * D:(t + 1) * D])
+                    outs[t].attach_torch(grad_dev[b][:, t * D:(t + 1) * D], grad=True)
+                m.forward()
+                fwd_ev[b].record(stream)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(fwd_ev[b])
+                    out_host.copy_(out_dev[b], non_blocking=True)
+                    d2h_ev[b].record(s_out)
+                m.zero_gradients()
+                m.backward()
+                m.update()
+                done_ev[b].record(stream)
+                issued[b] = True
+                if i > 0:
+                    d2h_ev[(i - 1) % NB].synchronize()       # the host now owns step i-1's pooled output
 
-        for i in range(NB):
-            e2e_step(i)
-        torch.cuda.synchronize()
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for i in range(args.e2e_steps):
-            e2e_step(NB + i)
-        s_out.synchronize()
-        stream.wait_stream(s_out)
-        stream.wait_stream(s_in)
-        e.record()
-        torch.cuda.synchronize()
-        e2e_ms = s.elapsed_time(e) / args.e2e_steps
-        line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
-                       "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
-                       "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
-                       "pipelining": "double-buffered: H2D of step i+1 and D2H of step i-1 overlap step i"}
-        m.sync()
-        del idx_host, grad_host, out_host, idx_dev, out_dev, grad_dev
+            for i in range(NB):
+                e2e_step(i)
+            torch.cuda.synchronize()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            for i in range(args.e2e_steps):
+                e2e_step(NB + i)
+            s_out.synchronize()
+            stream.wait_stream(s_out)
+            stream.wait_stream(s_in)
+            e.record()
+            torch.cuda.synchronize()
+            e2e_ms = s.elapsed_time(e) / args.e2e_steps
+            line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                           "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
+                           "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
+                           "pipelining": "double-buffered: H2D of step i+1 and D2H of step i-1 overlap step i"}
+            m.sync()
+            del idx_host, grad_host, out_host, idx_dev, out_dev, grad_dev
 
     if not args.no_cpu_baseline and rank == 0 and world == 1:
-        cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
-        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        with _Guard(line, "cpu_baseline"):
+            cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
         emit(line)
 
@@ -717,6 +719,23 @@ def run_sharded(args, w, rank, world, local_rank):
         emit(line)
     dist.barrier()
     dist.destroy_process_group()
+
+
+class _Guard(object):
+    """A failure inside an auxiliary measurement (the end-to-end loop, the CPU
+    baseline) is recorded under its key instead of losing the whole line."""
+
+    def __init__(self, line, key):
+        self.line, self.key = line, key
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, etype, evalue, tb):
+        if etype is not None and issubclass(etype, Exception):
+            self.line[self.key] = {"error": "%s: %s" % (etype.__name__, evalue)}
+            return True
+        return False
 
 
 _STDOUT = None
