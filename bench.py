@@ -24,6 +24,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "DLRM embedding-bag samples/sec fwd+bwd"
+CPU_KEYS = ("value", "unit", "cores", "kind", "sample", "value_single_thread", "host_cpus", "cpu_model")
 UNIT = "samples/s"
 
 
@@ -215,6 +216,20 @@ def cpu_reference_run(w, steps, warmup, row_cap, lr):
         step()
     dt = (time.perf_counter() - t0) / steps
     pool.shutdown()
+    # one step on a single thread as well: how the reference itself would run it
+    # (one Legion CPU task per op, no OpenMP anywhere in its tree)
+    t0 = time.perf_counter()
+    for t in order:
+        one_table(t)
+    dt1 = time.perf_counter() - t0
+    cpu_model = "unknown"
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                cpu_model = ln.split(":", 1)[1].strip()
+                break
+    except OSError:
+        pass
     sample = ("%s with every table capped at %d rows (%.1f GB of tables in host RAM), full batch %d, "
               "%d steps; forward = %s, backward + SGD = C restatement of embedding.cc:54-72 / "
               "optimizer_kernel.cu:23-41 on touched rows only (the reference's dense zero + dense "
@@ -223,7 +238,8 @@ def cpu_reference_run(w, steps, warmup, row_cap, lr):
                  "the reference's own AVX2 kernel (oracle/_ref)" if use_ref else "C restatement (oracle port)",
                  cores))
     return {"value": B / dt, "unit": UNIT, "cores": cores, "kind": "reference" if use_ref else "port",
-            "sample": sample, "ms_per_step": dt * 1e3}
+            "sample": sample, "ms_per_step": dt * 1e3, "value_single_thread": B / dt1,
+            "host_cpus": os.cpu_count(), "cpu_model": cpu_model}
 
 
 def run_reference_arm(args, w):
@@ -236,7 +252,7 @@ def run_reference_arm(args, w):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(args, w, 1),
-        "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "cpu_baseline": {k: cb[k] for k in CPU_KEYS},
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -441,6 +457,10 @@ def run_ours(args, w):
                           "frac_of_8tbs_nominal": step_bytes / ms_step / 1e6 / 8000.0},
         "phases": phases, "clocks": clocks, "gpu_launches": int(launches),
     }
+    with _Guard(line, "step_ms_percentiles"):      # spread of the individual steps
+        per = sorted(e[0].elapsed_time(e[3]) for e in evs)
+        line["step_ms_percentiles"] = {"p10": per[len(per) // 10], "p50": per[len(per) // 2],
+                                       "p90": per[(len(per) * 9) // 10], "n": len(per)}
 
     # ---- end to end: host buffers in, host buffers out, through the public API.
     # Every step copies its indices and upstream gradients from pinned host memory
@@ -518,7 +538,7 @@ def run_ours(args, w):
     if not args.no_cpu_baseline and rank == 0 and world == 1:
         with _Guard(line, "cpu_baseline"):
             cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
-            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline"] = {k: cb[k] for k in CPU_KEYS}
     if rank == 0:
         emit(line)
 
