@@ -7,15 +7,22 @@
  * the checker or the timed CPU baseline -- never as the thing being shipped.
  * The product path (dlrm_flexflow_b200/) has no CPU fallback.
  *
- * Parity status: PINNED against the reference's own CPU kernel.  The forward
- * restatement below is checked bit-for-bit against
+ * Parity status: PINNED against the reference's own CPU code, both halves.
+ * Forward: the restatement below is checked bit-for-bit against
  * /root/reference/src/ops/embedding_avx2.cc compiled in place into
  * oracle/_ref/libembedding_avx2.so (see oracle/Makefile and
  * tests/test_oracle.py), and against the golden vectors that kernel produced
- * (tests/golden/, generated by tests/golden/make_golden.py).  The reference
- * holds no test or fixture of its own for the embedding operator
- * (SURVEY.md F8), so backward / SGD are restatements of the reference source
- * lines cited at each function and are cross-checked against
+ * (tests/golden/embedding_avx2_golden.npz, made by tests/golden/make_golden.py).
+ * Backward: ffo_embed_backward_dense is checked bit-for-bit, for the case the
+ * reference's CPU code covers (one index per sample, SUM, accumulating into
+ * the gradient), against embed_backward_generic (src/ops/embedding.cc:54-72)
+ * compiled in place into oracle/_ref/libembed_backward_generic.so, and against
+ * the golden vectors it produced (tests/golden/embedding_bwd_golden.npz).
+ * The reference holds no test or fixture of its own for the embedding
+ * operator and no CPU code for bags longer than 1 in backward,
+ * for AVG's per-position g/L (CUDA only, src/ops/embedding.cu:213-218) or for
+ * the SGD update (CUDA only, src/runtime/optimizer_kernel.cu:23-41): those
+ * parts are restatements of the cited lines, cross-checked against
  * torch.nn.EmbeddingBag + torch.optim.SGD at 1e-5 (the reference test-suite's
  * own tolerance, src/ops/tests/test_harness.py:44-60).
  *

@@ -22,6 +22,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "libffemb_oracle.so")
 _REF = os.path.join(_HERE, "_ref", "libembedding_avx2.so")
+_REF_BWD = os.path.join(_HERE, "_ref", "libembed_backward_generic.so")
 _REF_SYM = "_Z45EmbeddingLookup_int64_t_float_float__avx2_fmaiiiiPKfPKlPKiS0_bPf"
 
 AGGR_MODE_SUM = 21  # include/ffconst.h:11-15
@@ -37,7 +38,8 @@ def build(force=False):
     if force or not os.path.exists(_LIB) or (
             os.path.getmtime(_LIB) < os.path.getmtime(os.path.join(_HERE, "ffemb_oracle.c"))):
         subprocess.check_call(["make", "-s", "-C", _HERE])
-    elif not os.path.exists(_REF) and os.path.exists("/root/reference/src/ops/embedding_avx2.cc"):
+    elif (not os.path.exists(_REF) or not os.path.exists(_REF_BWD)) and \
+            os.path.exists("/root/reference/src/ops/embedding_avx2.cc"):
         subprocess.check_call(["make", "-s", "-C", _HERE, "ref"])
 
 
@@ -105,6 +107,40 @@ def ref():
                        C.c_bool, _f32p]
         _ref = fn
     return _ref
+
+
+_ref_bwd = None
+
+
+def have_ref_bwd():
+    build()
+    return os.path.exists(_REF_BWD)
+
+
+def backward_ref(N, D, indices, g, gradW=None):
+    """The reference's own CPU backward, embed_backward_generic
+    (src/ops/embedding.cc:54-72), compiled in place by oracle/Makefile: one
+    index per sample (bag size 1), SUM, accumulating into gradW [N, D]."""
+    global _ref_bwd
+    if _ref_bwd is None:
+        if not have_ref_bwd():
+            raise RuntimeError("oracle/_ref/libembed_backward_generic.so absent: run `make -C oracle` "
+                               "in a container that has /root/reference")
+        fn = C.CDLL(_REF_BWD).embed_backward_generic
+        fn.restype = None
+        fn.argtypes = [_i64p, _i32p, _f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int]
+        _ref_bwd = fn
+    idx = np.ascontiguousarray(indices, dtype=np.int64).reshape(-1)
+    g = np.ascontiguousarray(g, dtype=np.float32)
+    B = g.shape[0]
+    assert idx.size == B and g.shape[1] == D and B * D < 2 ** 31
+    assert idx.size == 0 or (idx.min() >= 0 and idx.max() < N), "the reference does not check"
+    if gradW is None:
+        gradW = np.zeros((N, D), dtype=np.float32)
+    assert gradW.dtype == np.float32 and gradW.flags.c_contiguous
+    lengths = np.ones(B, dtype=np.int32)
+    _ref_bwd(_ip(idx), lengths.ctypes.data_as(_i32p), _fp(g), _fp(gradW), D, B, B, N)
+    return gradW
 
 
 def _lengths_arg(lengths):

@@ -10,6 +10,13 @@ Run in the authoring container (needs /root/reference):
   oracle/Makefile and called through oracle.oracle.forward_ref.  Covers the
   D=128/64/32 specialisations and the generic path (D=16, 20), bag sizes 1, 4
   and 32, ragged bags with empty ones, SUM and normalize_by_lengths (AVG).
+* embedding_bwd_golden.npz -- inputs and outputs of the reference's own CPU
+  backward embed_backward_generic (src/ops/embedding.cc:54-72), compiled in
+  place into oracle/_ref (only that Legion-free function) and called through
+  oracle.oracle.backward_ref: bag size 1, SUM, heavy duplication, D = 128, 64,
+  16 and 20, a fresh (zeroed) gradient and a second call accumulating into the
+  first one's result (the reference opens the gradient READ_WRITE,
+  src/ops/embedding.cu:350-352).
 * strategy_fixtures.json -- size, sha256 and decoded content of the three
   checked-in strategy files src/runtime/dlrm_strategy_*.pb (decoded with the
   protobuf runtime from the schema in src/runtime/strategy.proto, not with our
@@ -57,6 +64,27 @@ def embedding_cases():
             out[name + "_len"] = lengths
             out[name + "_sum"] = O.forward_ref(W, idx, lengths, O.AGGR_MODE_SUM)
             out[name + "_avg"] = O.forward_ref(W, idx, lengths, O.AGGR_MODE_AVG)
+    out["names"] = np.array(names)
+    return out
+
+
+def backward_cases():
+    rng = np.random.default_rng(20261107)
+    out, names = {}, []
+    for D in (128, 64, 16, 20):
+        for N, B in ((7, 130), (61, 97), (500, 64)):
+            idx = rng.integers(0, N, size=B).astype(np.int64)
+            g1 = rng.normal(size=(B, D)).astype(np.float32)
+            g2 = rng.normal(size=(B, D)).astype(np.float32)
+            G1 = O.backward_ref(N, D, idx, g1)
+            G2 = O.backward_ref(N, D, idx[::-1].copy(), g2, gradW=G1.copy())
+            name = "D%d_N%d_B%d" % (D, N, B)
+            names.append(name)
+            out[name + "_idx"] = idx
+            out[name + "_g1"] = g1
+            out[name + "_g2"] = g2
+            out[name + "_G1"] = G1
+            out[name + "_G2"] = G2      # second call (reversed indices) accumulated on top of G1
     out["names"] = np.array(names)
     return out
 
@@ -116,6 +144,8 @@ def strategy_fixtures():
 if __name__ == "__main__":
     assert O.have_ref(), "oracle/_ref missing: make -C oracle in a container with /root/reference"
     np.savez_compressed(os.path.join(HERE, "embedding_avx2_golden.npz"), **embedding_cases())
+    assert O.have_ref_bwd(), "oracle/_ref/libembed_backward_generic.so missing: make -C oracle"
+    np.savez_compressed(os.path.join(HERE, "embedding_bwd_golden.npz"), **backward_cases())
     with open(os.path.join(HERE, "strategy_fixtures.json"), "w") as f:
         json.dump(strategy_fixtures(), f, indent=1, sort_keys=True)
     print("wrote golden vectors")

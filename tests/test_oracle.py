@@ -49,6 +49,43 @@ def test_oracle_forward_matches_reference_kernel_live(oracle):
                 assert a.tobytes() == b.tobytes(), (D, L, aggr)
 
 
+BWD_GOLD = os.path.join(os.path.dirname(__file__), "golden", "embedding_bwd_golden.npz")
+
+
+def _bwd_cases():
+    z = np.load(BWD_GOLD)
+    for name in z["names"]:
+        name = str(name)
+        yield (name,) + tuple(z[name + s] for s in ("_idx", "_g1", "_g2", "_G1", "_G2"))
+
+
+@pytest.mark.parametrize("case", list(_bwd_cases()), ids=lambda c: c[0])
+def test_oracle_backward_matches_reference_golden(oracle, case):
+    """Bit-exact against vectors produced by the reference's own CPU backward,
+    embed_backward_generic (src/ops/embedding.cc:54-72): bag size 1, SUM, a
+    zeroed gradient and a second call accumulating on top of the first."""
+    name, idx, g1, g2, G1, G2 = case
+    N, D = G1.shape
+    got = oracle.backward_dense(N, D, idx.reshape(-1, 1), g1)
+    assert got.tobytes() == G1.tobytes()
+    got = oracle.backward_dense(N, D, idx[::-1].reshape(-1, 1), g2, gradW=got)
+    assert got.tobytes() == G2.tobytes()
+
+
+def test_oracle_backward_matches_reference_function_live(oracle):
+    """Same, against the compiled reference function itself on fresh shapes."""
+    if not oracle.have_ref_bwd():
+        pytest.skip("oracle/_ref/libembed_backward_generic.so not built (no /root/reference here)")
+    rng = np.random.default_rng(11)
+    for D in (128, 64, 32, 16, 4, 20, 7):
+        for N, B in ((3, 500), (97, 300), (4099, 128)):
+            idx = rng.integers(0, N, size=B)
+            g = rng.normal(size=(B, D)).astype(np.float32)
+            a = oracle.backward_dense(N, D, idx.reshape(-1, 1), g)
+            b = oracle.backward_ref(N, D, idx, g)
+            assert a.tobytes() == b.tobytes(), (D, N, B)
+
+
 def test_oracle_forward_fixed_equals_lengths(oracle):
     rng = np.random.default_rng(1)
     W = rng.normal(size=(50, 16)).astype(np.float32)
