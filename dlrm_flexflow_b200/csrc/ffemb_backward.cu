@@ -8,15 +8,15 @@
 // by work proportional to the lookups of the step:
 //   1. make_keys   key = table_row_base + row, val = table*B + bag
 //   2. stable LSD radix sort of (key, val) on the significant key bits
-//   3. reduce_l1   one sub-warp per chunk of 32 sorted positions: gradient
+//   3. reduce_kernel  one sub-warp per chunk of 32 sorted positions: gradient
 //                  rows added in sorted (= original (bag, position)) order; a
 //                  run inside the chunk is applied at once,
 //                  W[row,:] = fmaf(-lr, gsum, W[row,:]); runs cut by chunk
 //                  boundaries are chained in shared memory inside the block;
-//                  only runs that leave the block reach memory as partials
-//   4. reduce_l2 / reduce_l3   the block in which such a run starts adds the
-//                  following blocks' partials in order (one sub-warp for
-//                  short chains, one block for long ones) and applies it.
+//                  only runs that leave the block reach memory as partials,
+//                  and the block in which such a run ENDS looks back at the
+//                  earlier blocks' published partials, adds them in order and
+//                  applies the row -- all in the one launch.
 // No floating-point atomics; the result depends only on the inputs (bitwise
 // repeatable).  Rows whose lookups all fall in one chunk get the exact
 // sequential sum of the reference's CPU backward (src/ops/embedding.cc:54-72);
@@ -34,17 +34,12 @@ namespace ffemb {
 #endif
 std::atomic<int> g_sort_impl{FFEMB_DEFAULT_SORT};
 
-constexpr int kChunk = 32;  // sorted positions per sub-warp in reduce_l1
+constexpr int kChunk = 32;  // sorted positions per sub-warp in reduce_kernel
 constexpr int kBwdThreads = 256;
 #ifndef FFEMB_BU
 #define FFEMB_BU 8
 #endif
 constexpr int kBU = FFEMB_BU;     // positions whose rows are in flight together
-// reduce_l2 sums chains up to this many partials itself (one sub-warp, 8 loads
-// in flight); longer ones go to reduce_l3, where a whole block shares the chain.
-// Measured on C3 (whose 3-row table makes chains of 85 at D = 128): 32 -> update
-// phase 0.306 ms, 128 -> 0.313 ms, so the second kernel pays for itself early.
-constexpr int kShortChain = 32;
 #ifndef FFEMB_L1_MINBLOCKS
 #define FFEMB_L1_MINBLOCKS 2
 #endif
@@ -80,11 +75,10 @@ struct BwdParams {
   Matrix grad;
   const void *keys;
   const uint32_t *vals;
-  float *part0;      // [blocks][D] partial of the run that enters a level-1 block
-  float *part1;      // [blocks][D] partial of the run that leaves it
-  int *counters;     // [0] chains, [1] long chains
-  int *owners;       // blocks in which a leaving run starts
-  int2 *long_owners; // (first block, last block) of chains longer than kShortChain
+  float *part0;      // [blocks][D] partial of the run that enters a block
+  float *part1;      // [blocks][D] partial of the run that starts in a block and leaves it
+  uint32_t *status;  // [blocks] 0 -> 1 once the block's partials are published; [blocks]: block ticket
+  int *err;
   int n;
   int T;
   int B;
@@ -170,6 +164,17 @@ struct Cols {
     if (d + 96 < D) v.w = row[d + 96];
     return v;
   }
+  // partials published by other blocks: read at L2, never from this SM's L1
+  __device__ __forceinline__ float4 ld_cg(const float *row) const {
+    if (VEC) return __ldcg((const float4 *)(row + gl * 4));
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int d = d0 + gl;
+    if (d < D) v.x = __ldcg(row + d);
+    if (d + 32 < D) v.y = __ldcg(row + d + 32);
+    if (d + 64 < D) v.z = __ldcg(row + d + 64);
+    if (d + 96 < D) v.w = __ldcg(row + d + 96);
+    return v;
+  }
   __device__ __forceinline__ void st(float *row, const float4 &v) const {
     if (VEC) {
       st_row(row + gl * 4, v);
@@ -212,7 +217,7 @@ __device__ __forceinline__ int table_of(const BwdParams &p, KeyT key) {
 }
 
 // ---------------------------------------------------------------------------
-// 3. level-1 segmented reduce + SGD.
+// 3. segmented reduce + SGD, one launch.
 //
 // Per chunk of 32 sorted positions, each lane of the sub-warp first works out
 // its own positions' bookkeeping (key, neighbours' keys, table, gradient-row
@@ -223,30 +228,60 @@ __device__ __forceinline__ int table_of(const BwdParams &p, KeyT key) {
 // order.  Runs cut by a chunk boundary leave a partial in shared memory;
 // after one barrier the sub-warp in whose chunk such a run starts adds the
 // following chunks' partials in order, so only runs that leave the BLOCK
-// (256/G chunks) reach global memory as partials.
+// (256/G chunks) reach global memory as partials: part0[b] for the run that
+// enters block b, part1[b] for the run that starts in b and leaves it.
+//
+// Runs that cross block boundaries ("chains") are completed by the block in
+// which they END, decoupled-look-back style: every block publishes its
+// partials and then raises status[b]; the end block finds the chain's first
+// block by galloping + bisecting over the (sorted) first keys of the blocks,
+// waits for the status words of the blocks before it, and adds
+// part1[first], part0[first+1 .. end] in that order.  Blocks take their
+// number from a ticket counter, so every block a waiter looks back at has
+// already started: waits only ever point at lower tickets and cannot cycle.
 // ---------------------------------------------------------------------------
 constexpr int kHasLead = 1;   // first run of the chunk started before the chunk
 constexpr int kLeadCont = 2;  // ... and also continues past the end of the chunk
 constexpr int kHasTrail = 4;  // last run started in the chunk and continues past it
 
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long bwd_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 template <typename KeyT, int G, bool VEC>
 __global__ void __launch_bounds__(kBwdThreads, FFEMB_L1_MINBLOCKS)
-reduce_l1_kernel(const __grid_constant__ BwdParams p) {
+reduce_kernel(const __grid_constant__ BwdParams p) {
   constexpr int U = kBU;
   constexpr int S = kBwdThreads / G;  // chunks (sub-warps) per block
   constexpr int KPL = kChunk / G;     // positions per lane
+  constexpr int kSpan = S * kChunk;   // positions per block
   constexpr KeyT kInv = KeyTraits<KeyT>::kInvalid;
   static_assert(G >= 4 && G <= 32, "sub-warp of 4..32 lanes");
   __shared__ float4 s_lead[S][G];
   __shared__ float4 s_trail[S][G];
   __shared__ int s_flags[S];
+  __shared__ int s_bid;
   const KeyT *__restrict__ keys = (const KeyT *)p.keys;
   const int s = threadIdx.x / G, gl = threadIdx.x % G;
   const int subshift = (threadIdx.x & 31) / G * G;
   const unsigned gmask = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
   const unsigned submask = gmask << subshift;
   const int n = p.n;
-  const int i0 = (blockIdx.x * S + s) * kChunk;
+  const int nblocks = gridDim.x;
+  if (threadIdx.x == 0) s_bid = (int)atomicAdd(p.status + nblocks, 1u);
+  __syncthreads();
+  const int bid = s_bid;
+  const int i0 = (bid * S + s) * kChunk;
   const int cnt = n - i0 < kChunk ? n - i0 : kChunk;  // positions in this chunk (<= 0: none)
   const int D = p.D;
 
@@ -377,7 +412,7 @@ reduce_l1_kernel(const __grid_constant__ BwdParams p) {
         add4(a, s_lead[s2][gl]);
         cont = s_flags[s2] & kLeadCont;
       }
-      cols.st(p.part0 + (int64_t)blockIdx.x * D, a);
+      cols.st(p.part0 + (int64_t)bid * D, a);
     }
     if (flags & kHasTrail) {
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -387,126 +422,78 @@ reduce_l1_kernel(const __grid_constant__ BwdParams p) {
         add4(a, s_lead[s2][gl]);
         cont = s_flags[s2] & kLeadCont;
       }
-      if (cont) {  // leaves the block: level 2 finishes it
-        cols.st(p.part1 + (int64_t)blockIdx.x * D, a);
-        if (gl == 0 && d0 == 0) p.owners[atomicAdd(&p.counters[0], 1)] = blockIdx.x;
-      } else {
+      if (cont)  // leaves the block: the block in which it ends completes it
+        cols.st(p.part1 + (int64_t)bid * D, a);
+      else
         cols.st(wlast, sgd_row(p.lr, a, cols.ld(wlast)));
-      }
     }
     if (!VEC) __syncthreads();  // shared partials are reused by the next column tile
   }
-}
 
-// ---------------------------------------------------------------------------
-// 4. level-2: runs that cross block boundaries ("chains").  One sub-warp per
-// chain: finds the last block the run reaches (keys are sorted: gallop, then
-// bisect), adds the entering partials of the following blocks in order and
-// applies the update.  Chains longer than kShortChain go to reduce_l3.
-// ---------------------------------------------------------------------------
-template <typename KeyT, int G, bool VEC>
-__global__ void __launch_bounds__(kBwdThreads)
-reduce_l2_kernel(const __grid_constant__ BwdParams p) {
-  constexpr int S = kBwdThreads / G;
-  constexpr int kSpan = S * kChunk;
-  const KeyT *__restrict__ keys = (const KeyT *)p.keys;
-  const int n = p.n, D = p.D;
-  const int nspans = (n + kSpan - 1) / kSpan;
-  const int count = p.counters[0];
-  Cols<VEC> cols{(int)(threadIdx.x % G), 0, D};
-  for (int o = blockIdx.x * S + threadIdx.x / G; o < count; o += gridDim.x * S) {
-    const int c = p.owners[o];
-    const KeyT key = keys[(c + 1) * kSpan - 1];
-    // last span whose first key is still `key` (span c+1 is, by construction)
-    int lo = c + 1, step = 1;
-    while (lo + step < nspans && keys[(int64_t)(lo + step) * kSpan] == key) {
-      lo += step;
-      step *= 2;
-    }
-    int hi = lo + step < nspans ? lo + step : nspans;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (keys[(int64_t)mid * kSpan] == key)
-        lo = mid;
-      else
-        hi = mid;
-    }
-    const int last = lo;
-    if (last - c > kShortChain) {
-      if (threadIdx.x % G == 0) p.long_owners[atomicAdd(&p.counters[1], 1)] = make_int2(c, last);
-      continue;
-    }
-    const int t = table_of(p, key);
-    float *wrow = p.t[t].W + ((int64_t)key - p.t[t].row_base) * D;
-    for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
-      cols.d0 = d0;
-      const float4 w = cols.ld(wrow);
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      add4(acc, cols.ld(p.part1 + (int64_t)c * D));
-      for (int b = c + 1; b <= last; b += 8) {
-        float4 v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (b + j <= last) v[j] = cols.ld(p.part0 + (int64_t)(b + j) * D);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (b + j <= last) add4(acc, v[j]);
-      }
-      cols.st(wrow, sgd_row(p.lr, acc, w));
-    }
+  // ---- publish this block's partials ----------------------------------------
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_gpu(p.status + bid, 1u);
+
+  // ---- complete the chain that ends in this block ---------------------------
+  if (s != 0 || !(s_flags[0] & kHasLead)) return;
+  for (int s2 = 0; s2 < S; ++s2) {
+    if (!(s_flags[s2] & kLeadCont)) break;
+    if (s2 == S - 1) return;  // the entering run also leaves the block: a later block ends it
   }
-}
-
-// ---------------------------------------------------------------------------
-// 5. level-3: long chains, one block each.  The sub-warps sum contiguous
-// slices of the chain, then sub-warp 0 adds the slices in order.
-// ---------------------------------------------------------------------------
-template <typename KeyT, int G, bool VEC>
-__global__ void __launch_bounds__(kBwdThreads)
-reduce_l3_kernel(const __grid_constant__ BwdParams p) {
-  constexpr int S = kBwdThreads / G;
-  constexpr int kSpan = S * kChunk;
-  __shared__ float4 s_part[S][G];
-  const KeyT *__restrict__ keys = (const KeyT *)p.keys;
-  const int D = p.D;
-  const int s = threadIdx.x / G, gl = threadIdx.x % G;
-  const int count = p.counters[1];
-  Cols<VEC> cols{gl, 0, D};
-  for (int o = blockIdx.x; o < count; o += gridDim.x) {
-    const int2 cl = p.long_owners[o];
-    const int c = cl.x, len = cl.y - cl.x;  // partials part0[c+1 .. c+len]
-    const int per = (len + S - 1) / S;
-    const int b0 = c + 1 + s * per;
-    const int b1 = b0 + per < c + 1 + len ? b0 + per : c + 1 + len;
-    for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
-      cols.d0 = d0;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int b = b0; b < b1; b += 8) {
-        float4 v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (b + j < b1) v[j] = cols.ld(p.part0 + (int64_t)(b + j) * D);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (b + j < b1) add4(acc, v[j]);
-      }
-      s_part[s][gl] = acc;
-      __syncthreads();
-      if (s == 0) {
-        const KeyT key = keys[(c + 1) * kSpan - 1];
-        const int t = table_of(p, key);
-        float *wrow = p.t[t].W + ((int64_t)key - p.t[t].row_base) * D;
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-        add4(a, cols.ld(p.part1 + (int64_t)c * D));
-        for (int s2 = 0; s2 < S; ++s2) add4(a, s_part[s2][gl]);
-        cols.st(wrow, sgd_row(p.lr, a, cols.ld(wrow)));
-      }
-      __syncthreads();
+  const KeyT key = keys[(int64_t)bid * kSpan];  // the entering run's key
+  // first block whose first key is `key` (the blocks' first keys are sorted)
+  int hi = bid, lo = -1;
+  for (int step = 1;; step *= 2) {
+    const int j = hi - step;
+    if (j < 0) break;
+    if (keys[(int64_t)j * kSpan] != key) {
+      lo = j;
+      break;
     }
+    hi = j;
+  }
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (keys[(int64_t)mid * kSpan] == key)
+      hi = mid;
+    else
+      lo = mid;
+  }
+  // the run starts in block hi at its first position, or inside block hi - 1
+  const int c = (hi > 0 && keys[(int64_t)hi * kSpan - 1] == key) ? hi - 1 : hi;
+  {
+    const unsigned long long t0 = bwd_timer_ns();
+    for (int j = c + gl; j < bid; j += G) {
+      while (ld_acquire_gpu(p.status + j) == 0u) {
+        if (bwd_timer_ns() - t0 > 2000000000ull) {  // 2 s: a lower ticket never published
+          if (p.err) *p.err = FFEMB_ERR_CUDA;
+          break;
+        }
+        __nanosleep(32);
+      }
+    }
+    __syncwarp(submask);
+  }
+  const int t = table_of(p, key);
+  float *wrow = p.t[t].W + ((int64_t)key - p.t[t].row_base) * D;
+  for (int d0 = 0; d0 < (VEC ? 1 : D); d0 += 128) {
+    cols.d0 = d0;
+    const float4 w = cols.ld(wrow);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    add4(acc, cols.ld_cg(p.part1 + (int64_t)c * D));
+    for (int b = c + 1; b <= bid; b += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (b + j <= bid) v[j] = cols.ld_cg(p.part0 + (int64_t)(b + j) * D);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (b + j <= bid) add4(acc, v[j]);
+    }
+    cols.st(wrow, sgd_row(p.lr, acc, w));
   }
 }
 
@@ -515,15 +502,8 @@ static void launch_reduce(const BwdParams &p, cudaStream_t s) {
   constexpr int per_block = kBwdThreads / G;
   const int64_t chunks = ((int64_t)p.n + kChunk - 1) / kChunk;
   const int64_t blocks = (chunks + per_block - 1) / per_block;
-  reduce_l1_kernel<KeyT, G, VEC><<<(unsigned)blocks, kBwdThreads, 0, s>>>(p);
+  reduce_kernel<KeyT, G, VEC><<<(unsigned)blocks, kBwdThreads, 0, s>>>(p);
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  if (blocks > 1) {
-    // grids sized to the machine (148 SMs); both kernels stride over their lists
-    const int64_t want = (blocks + per_block - 1) / per_block;
-    reduce_l2_kernel<KeyT, G, VEC><<<(unsigned)(want < 148 * 4 ? want : 148 * 4), kBwdThreads, 0, s>>>(p);
-    reduce_l3_kernel<KeyT, G, VEC><<<(unsigned)(blocks < 148 * 2 ? blocks : 148 * 2), kBwdThreads, 0, s>>>(p);
-    g_launches.fetch_add(2, std::memory_order_relaxed);
-  }
 }
 
 template <typename KeyT>
@@ -548,8 +528,8 @@ struct Workspace {
   void *sort_tmp;
   size_t sort_tmp_bytes;
   float *part0, *part1;
-  int *counters, *owners;
-  int2 *long_owners;
+  uint32_t *status;  // [blocks + 1]: per-block "published" words, then the ticket counter
+  size_t status_bytes;
   size_t total;
 };
 
@@ -594,9 +574,8 @@ static Workspace carve(void *base, int64_t n, int64_t total_entries, int D) {
   w.sort_tmp = take(w.sort_tmp_bytes);
   w.part0 = (float *)take((size_t)blocks * D * 4);
   w.part1 = (float *)take((size_t)blocks * D * 4);
-  w.counters = (int *)take(256);
-  w.owners = (int *)take((size_t)blocks * sizeof(int));
-  w.long_owners = (int2 *)take((size_t)blocks * sizeof(int2));
+  w.status_bytes = (size_t)(blocks + 1) * sizeof(uint32_t);
+  w.status = (uint32_t *)take(w.status_bytes);
   w.total = off;
   return w;
 }
@@ -608,8 +587,8 @@ struct Group {  // one batched launch group (<= kMaxTables tables)
   int64_t total_entries;  // rows in the group
 };
 
-static int check_lookups(const char *who, const ffemb_lookup_t *lookups, int num_tables,
-                         int batch, int out_dim) {
+int check_lookups(const char *who, const ffemb_lookup_t *lookups, int num_tables, int batch,
+                  int out_dim) {
   if (!lookups || num_tables < 0)
     return fail(FFEMB_ERR_INVALID_ARGUMENT, std::string(who) + ": lookups is NULL");
   if (batch < 0 || out_dim <= 0)
@@ -673,7 +652,7 @@ static int sort_group(const ffemb_lookup_t *lookups, int T, int batch, const Wor
 }
 
 static int update_group(const ffemb_lookup_t *lookups, int T, int batch, int out_dim, int avg,
-                        const Matrix &grad, float lr, const Workspace &w, const Group &g,
+                        const Matrix &grad, float lr, const Workspace &w, const Group &g, int *err,
                         cudaStream_t s) {
   if (g.n == 0) return FFEMB_OK;
   BwdParams bp;
@@ -692,16 +671,16 @@ static int update_group(const ffemb_lookup_t *lookups, int T, int batch, int out
   bp.vals = w.vals_b;
   bp.part0 = w.part0;
   bp.part1 = w.part1;
-  bp.counters = w.counters;
-  bp.owners = w.owners;
-  bp.long_owners = w.long_owners;
+  bp.status = w.status;
+  bp.err = err;
   bp.n = (int)g.n;
   bp.T = T;
   bp.B = batch;
   bp.D = out_dim;
   bp.avg = avg;
   bp.lr = lr;
-  FFEMB_CUDA_OK(cudaMemsetAsync(w.counters, 0, 2 * sizeof(int), s));
+  // every block's "published" word and the ticket counter start from zero
+  FFEMB_CUDA_OK(cudaMemsetAsync(w.status, 0, w.status_bytes, s));
   if (wide_keys(g.total_entries))
     launch_reduce_g<uint64_t>(bp, vec, s);
   else
@@ -748,7 +727,7 @@ static int backward_impl(int phases, const ffemb_lookup_t *lookups, int num_tabl
       if (rc) return rc;
     }
     if (phases & kUpdate)
-      if (int rc = update_group(lookups + t0, T, batch, out_dim, avg, gm, lr, w, g, s)) return rc;
+      if (int rc = update_group(lookups + t0, T, batch, out_dim, avg, gm, lr, w, g, err, s)) return rc;
   }
   return FFEMB_OK;
 }
@@ -823,10 +802,11 @@ extern "C" int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tab
 //     make that first call outside any stream capture;
 //   * all calls on one device share the one array.  It still holds whatever
 //     the previous call left there; the only part that has to start from
-//     zero -- the two chain counters -- is cleared by every call on its
-//     stream before use.  Two calls that overlap on the GPU (different
-//     streams, or different host threads) would trample each other's keys
-//     and partial sums: serialise them.
+//     zero -- the blocks' "published" words and the ticket counter of the
+//     reduce kernel -- is cleared by every call on its stream before use.
+//     Two calls that overlap on the GPU (different streams, or different host
+//     threads) would trample each other's keys and partial sums: serialise
+//     them.
 // Nothing here calls cudaMalloc, cudaFree or a library routine that does.
 // ---------------------------------------------------------------------------
 #define FFEMB_STATIC_SCRATCH_BYTES (8u << 20)
@@ -838,8 +818,9 @@ static __device__ __align__(256) unsigned char g_static_scratch[FFEMB_STATIC_SCR
 namespace ffemb {
 
 constexpr int kMaxDevices = 64;
-static void *g_static_scratch_ptr[kMaxDevices];  // device address of the array, per device
-static std::atomic<bool> g_static_scratch_ready[kMaxDevices];
+// device address of the array, per device; nullptr = not looked up yet.  Two host
+// threads making their first call at once both store the same value.
+static std::atomic<void *> g_static_scratch_ptr[kMaxDevices];
 
 // Device address of g_static_scratch on the current device (looked up once).
 static int static_scratch(void **ptr) {
@@ -847,13 +828,13 @@ static int static_scratch(void **ptr) {
   FFEMB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= kMaxDevices)
     return fail(FFEMB_ERR_UNSUPPORTED, "backward_sgd_static: device ordinal out of range");
-  if (!g_static_scratch_ready[dev].load(std::memory_order_acquire)) {
-    void *p = nullptr;
+  void *p = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
     FFEMB_CUDA_OK(cudaGetSymbolAddress(&p, g_static_scratch));
-    g_static_scratch_ptr[dev] = p;
-    g_static_scratch_ready[dev].store(true, std::memory_order_release);
+    if (!p) return fail(FFEMB_ERR_CUDA, "backward_sgd_static: the scratch array has no device address");
+    g_static_scratch_ptr[dev].store(p, std::memory_order_release);
   }
-  *ptr = g_static_scratch_ptr[dev];
+  *ptr = p;
   return FFEMB_OK;
 }
 

@@ -83,6 +83,11 @@ __device__ __forceinline__ void add4(float4 &a, const float4 &v) {
   a.w += v.w;
 }
 
+// Host-side validation shared by the forward and backward entry points: the
+// same malformed lookups are refused by both (ffemb_backward.cu).
+int check_lookups(const char *who, const ffemb_lookup_t *lookups, int num_tables, int batch,
+                  int out_dim);
+
 inline int to_matrix(const ffemb_matrix_t *in, int batch, Matrix *out) {
   if (!in) return fail(FFEMB_ERR_INVALID_ARGUMENT, "matrix is NULL");
   if (in->num_parts < 1 || in->num_parts > kMaxParts)

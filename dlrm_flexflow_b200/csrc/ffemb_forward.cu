@@ -219,10 +219,7 @@ extern "C" int ffemb_embed_forward(const ffemb_lookup_t *lookups, int num_tables
                                    int batch, int out_dim, enum AggrMode aggr,
                                    const ffemb_matrix_t *out, int *err_flag,
                                    void *stream) {
-  if (!lookups || num_tables < 0)
-    return fail(FFEMB_ERR_INVALID_ARGUMENT, "embed_forward: lookups is NULL");
-  if (batch < 0 || out_dim <= 0)
-    return fail(FFEMB_ERR_INVALID_ARGUMENT, "embed_forward: bad batch/out_dim");
+  if (int rc = check_lookups("embed_forward", lookups, num_tables, batch, out_dim)) return rc;
   if (aggr != AGGR_MODE_SUM && aggr != AGGR_MODE_AVG)
     return fail(FFEMB_ERR_INVALID_ARGUMENT,
                 "embed_forward: aggr must be AGGR_MODE_SUM or AGGR_MODE_AVG");
@@ -240,11 +237,6 @@ extern "C" int ffemb_embed_forward(const ffemb_lookup_t *lookups, int num_tables
   for (int r = 0; r < p.out.num_parts; ++r) vec = vec && aligned16(p.out.base[r]);
   for (int t = 0; t < num_tables; ++t) {
     const ffemb_lookup_t &l = lookups[t];
-    if (!l.weight || (!l.indices && l.num_indices > 0) || l.num_entries <= 0)
-      return fail(FFEMB_ERR_INVALID_ARGUMENT, "embed_forward: table " +
-                                                  std::to_string(t) + " has a NULL pointer or no rows");
-    if (!l.offsets && l.bag_size < 0)
-      return fail(FFEMB_ERR_INVALID_ARGUMENT, "embed_forward: negative bag_size");
     vec = vec && aligned16(l.weight) && l.col % 4 == 0;
   }
 

@@ -650,6 +650,7 @@ extern "C" int ffemb_tensor_set_int64(ffemb_tensor_t h, ffemb_model_t model, con
   }
   FFEMB_CUDA_OK(cudaMemcpyAsync(t->data.ptr, data, n * sizeof(int64_t), cudaMemcpyHostToDevice,
                                 m->stream));
+  m->presorted = false;  // keys sorted during forward() belong to the old contents
   return FFEMB_OK;
 }
 
@@ -704,6 +705,7 @@ extern "C" int ffemb_tensor_attach_device_ptr(ffemb_tensor_t h, void *device_ptr
     cudaFree(b.ptr);
   }
   b = Buffer{device_ptr, ld, false};
+  if (!t->producer) t->model->presorted = false;  // an index tensor changed under a finished sort
   return FFEMB_OK;
 }
 extern "C" void *ffemb_tensor_get_device_ptr(ffemb_tensor_t h, bool grad) {

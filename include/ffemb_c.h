@@ -77,7 +77,11 @@ typedef struct ffemb_lookup_t {
   const int64_t *indices; /* device, flattened [bag][position]               */
   const int64_t *offsets; /* device, batch+1 CSR bag offsets; NULL = fixed   */
   int64_t num_entries;    /* rows of the table                               */
-  int64_t num_indices;    /* indices in this batch (batch*bag_size if fixed) */
+  int64_t num_indices;    /* indices in this batch: exactly batch*bag_size
+                             for fixed bags (checked, both directions);
+                             exactly offsets[batch] for CSR bags (device
+                             data, NOT checked: positions past offsets[batch]
+                             would be sorted and applied uninitialised)      */
   int64_t col;            /* offset (floats) of this table's block from the
                              start of a row of the output / gradient matrix:
                              its first column in a [batch][T*D] concat
@@ -171,13 +175,17 @@ int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tables,
  * library image -- ffemb_static_scratch_bytes() = 8 MiB of device memory that
  * every GPU which loads the library keeps until the process exits.
  *   - A batch needing more scratch than that (about 250k lookups at out_dim
- *     128; ffemb_embed_backward_workspace_bytes gives the need) is refused
- *     with FFEMB_ERR_WORKSPACE_TOO_SMALL.
- *   - The first call on each device resolves the array's device address;
- *     make that call before any stream capture begins.
+ *     128) is refused with FFEMB_ERR_WORKSPACE_TOO_SMALL.  The need is the
+ *     exact layout size, ffemb_embed_backward_workspace_bytes() minus the
+ *     1 MiB of slack that function adds for callers with several launch
+ *     groups; at most 64 tables per call.
+ *   - The first call on each device resolves the array's device address
+ *     (two host threads may make it at the same time); make that call before
+ *     any stream capture begins.
  *   - All calls on a device share the array and find the previous call's
- *     data in it; the chain counters, the only part that must start at zero,
- *     are cleared by each call.  Calls that overlap on the GPU race on the
+ *     data in it; the reduce kernel's per-block status words and its ticket
+ *     counter, the only part that must start at zero, are cleared by each
+ *     call.  Calls that overlap on the GPU race on the
  *     array: issue them one after the other on one stream.
  * Inputs, outputs and results are those of ffemb_embed_backward_sgd. */
 size_t ffemb_static_scratch_bytes(void);

@@ -8,7 +8,10 @@ instead.  These tests call it through the C-ABI, twice in a row on one device
 (the second call finds the first call's leftovers in the shared array), and
 require the tables to match what the workspace-taking entry point produces
 from the same inputs, at the tolerance the other backward tests use
-(rtol = atol = 1e-5).  The file name keeps it last in collection order so a
+(rtol = atol = 1e-5), and what the CPU oracle computes.  They also check the
+property the entry point exists for -- repeated calls leave the amount of
+device memory in use exactly where it was -- and both sides of its size
+limit.  The file name keeps it last in collection order so a
 `pytest -x` run has exercised everything else before it gets here; it also
 passes on its own in a fresh process.
 """
@@ -70,6 +73,68 @@ def test_static_entry_matches_workspace_entry_twice_in_a_row(K):
         for t in range(T):
             assert not np.array_equal(got[t], Ws[t])            # the update happened
             np.testing.assert_allclose(got[t], ref[t], **TOL)
+
+
+def test_static_entry_matches_the_oracle(K, oracle):
+    T, D, B, L = 3, 64, 2048, 2
+    Ws, idx, g = _inputs(31, T, D, B, L, True)
+    _, got = _both(K, Ws, idx, g, AVG, 0.05)
+    for t in range(T):
+        _, want = oracle.step(Ws[t], idx[t], g[:, t * D:(t + 1) * D], 0.05, aggr=oracle.AGGR_MODE_AVG)
+        np.testing.assert_allclose(got[t], want, **TOL)
+
+
+def test_static_entry_allocates_no_device_memory(K):
+    """What the entry point is for: after the first call on the device (which
+    looks the array's address up) further calls must not move the driver's
+    free-memory figure nor torch's allocator."""
+    T, D, B, L = 2, 128, 8192, 1
+    Ws, idx, g = _inputs(5, T, D, B, L, False)
+    di = [torch.from_numpy(i).cuda() for i in idx]
+    dg = torch.from_numpy(g).cuda()
+    w = [torch.from_numpy(x).cuda() for x in Ws]
+    lk = K.make_lookups(w, di)
+    K.embed_backward_sgd_static(lk, B, D, SUM, dg, 0.01)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    for _ in range(5):
+        K.embed_backward_sgd_static(lk, B, D, SUM, dg, 0.01)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0
+    assert (torch.cuda.memory_allocated(), torch.cuda.memory_reserved()) == (alloc0, reserved0)
+
+
+def test_static_entry_size_limit_both_sides(K):
+    """The limit is the exact scratch layout: workspace_bytes() minus the 1 MiB
+    of slack that function adds.  The largest batch that fits runs and matches
+    the workspace entry point; one past the limit is refused."""
+    from dlrm_flexflow_b200 import FFEmbError
+    D, rows = 16, 1000
+    need = lambda b: K.backward_workspace_bytes(b, rows, D) - (1 << 20)
+    lo, hi = 1024, 4 << 20
+    assert need(lo) <= K.static_scratch_bytes() < need(hi)
+    while hi - lo > 1:
+        mid = (lo + hi) // 2
+        lo, hi = (mid, hi) if need(mid) <= K.static_scratch_bytes() else (lo, mid)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(3)
+    for B, fits in ((lo, True), (hi, False)):
+        idx = torch.randint(0, rows, (B, 1), device="cuda", generator=gen)
+        g = torch.randn(B, D, device="cuda", generator=gen)
+        w0 = torch.randn(rows, D, device="cuda", generator=gen)
+        wa, wb = w0.clone(), w0.clone()
+        if fits:
+            K.embed_backward_sgd(K.make_lookups([wa], [idx]), B, D, SUM, g, 0.01, K.alloc_workspace(B, rows, D))
+            K.embed_backward_sgd_static(K.make_lookups([wb], [idx]), B, D, SUM, g, 0.01)
+            torch.cuda.synchronize()
+            np.testing.assert_allclose(wb.cpu().numpy(), wa.cpu().numpy(), **TOL)
+        else:
+            with pytest.raises(FFEmbError) as e:
+                K.embed_backward_sgd_static(K.make_lookups([wb], [idx]), B, D, SUM, g, 0.01)
+            assert e.value.status == 5
+            assert torch.equal(wb, w0)
 
 
 def test_static_entry_repeats_itself_bit_for_bit(K):
