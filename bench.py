@@ -606,6 +606,7 @@ def run_sharded(args, w, rank, world, local_rank):
             ev[2].record()
 
     launches_per_step = None
+    g_fwd = g_bwd = None
     if args.graph and args.exchange == "p2p":
         # forward (+ its exchange and barrier) and backward (+ barriers) as two
         # CUDA graphs over fixed index buffers; the peer barrier keeps its count
@@ -734,11 +735,31 @@ def run_sharded(args, w, rank, world, local_rank):
                        "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
                        "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
                        "note": "bytes are per rank; every rank copies its own slice"}
-    sh.close()
     if rank == 0:
         emit(line)
+    # Teardown order matters: captured graphs hold references into the process
+    # group's communicator and into the peer mappings, so they go first; then
+    # the peer mappings (every rank past its last kernel), then the group.
+    _arm_exit_watchdog(60.0)
+    g_fwd = g_bwd = None      # noqa: F841
+    torch.cuda.synchronize()
+    dist.barrier()
+    sh.close()
     dist.barrier()
     dist.destroy_process_group()
+
+
+def _arm_exit_watchdog(seconds):
+    """The JSON line is out; if tearing the process group down ever wedges
+    (round 1: a rank sat in communicator destruction until the driver killed
+    it after 870 s), leave with status 0 instead of holding the launcher."""
+    def _bail():
+        sys.stderr.write("bench.py: teardown did not finish within %.0f s, exiting\n" % seconds)
+        sys.stderr.flush()
+        os._exit(0)
+    t = threading.Timer(seconds, _bail)
+    t.daemon = True
+    t.start()
 
 
 class _Guard(object):
