@@ -24,13 +24,17 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include "ffemb_common.cuh"
+#include "ffemb_csort.cuh"
 #include "ffemb_sort.cuh"
 
 namespace ffemb {
 
-// 0: CUB DeviceRadixSort (library), 1: the segmented per-table sort of ffemb_sort.cuh
+// 0: CUB DeviceRadixSort (library); 1: the segmented per-table sort of ffemb_sort.cuh
+// (three launches per pass, through global memory); 2: the one-launch on-chip
+// cluster sort of ffemb_csort.cuh where every table's segment fits (<= 65536
+// lookups per table), else 1.  Launch groups with 2^32-1 rows or more: always 0.
 #ifndef FFEMB_DEFAULT_SORT
-#define FFEMB_DEFAULT_SORT 0
+#define FFEMB_DEFAULT_SORT 2
 #endif
 std::atomic<int> g_sort_impl{FFEMB_DEFAULT_SORT};
 
@@ -77,7 +81,7 @@ struct BwdParams {
   const uint32_t *vals;
   float *part0;      // [blocks][D] partial of the run that enters a block
   float *part1;      // [blocks][D] partial of the run that starts in a block and leaves it
-  uint32_t *status;  // [blocks] 0 -> 1 once the block's partials are published; [blocks]: block ticket
+  uint32_t *status;  // [2][blocks] 0 -> 1 once part0[b] / part1[b] is published
   int *err;
   int n;
   int T;
@@ -232,13 +236,12 @@ __device__ __forceinline__ int table_of(const BwdParams &p, KeyT key) {
 // enters block b, part1[b] for the run that starts in b and leaves it.
 //
 // Runs that cross block boundaries ("chains") are completed by the block in
-// which they END, decoupled-look-back style: every block publishes its
-// partials and then raises status[b]; the end block finds the chain's first
-// block by galloping + bisecting over the (sorted) first keys of the blocks,
-// waits for the status words of the blocks before it, and adds
-// part1[first], part0[first+1 .. end] in that order.  Blocks take their
-// number from a ticket counter, so every block a waiter looks back at has
-// already started: waits only ever point at lower tickets and cannot cycle.
+// which they END, decoupled-look-back style: the sub-warp that stores a
+// partial then raises its status word (fence, then a relaxed store); the end
+// block finds the chain's first block by galloping + bisecting over the
+// (sorted) first keys of the blocks, waits for the status words of the blocks
+// before it, and adds part1[first], part0[first+1 .. end] in that order.
+// Waits only ever point at lower block indices and cannot cycle.
 // ---------------------------------------------------------------------------
 constexpr int kHasLead = 1;   // first run of the chunk started before the chunk
 constexpr int kLeadCont = 2;  // ... and also continues past the end of the chunk
@@ -249,8 +252,8 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_gpu(uint32_t *p, uint32_t v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_gpu(uint32_t *p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned long long bwd_timer_ns() {
   unsigned long long t;
@@ -270,17 +273,17 @@ reduce_kernel(const __grid_constant__ BwdParams p) {
   __shared__ float4 s_lead[S][G];
   __shared__ float4 s_trail[S][G];
   __shared__ int s_flags[S];
-  __shared__ int s_bid;
   const KeyT *__restrict__ keys = (const KeyT *)p.keys;
   const int s = threadIdx.x / G, gl = threadIdx.x % G;
   const int subshift = (threadIdx.x & 31) / G * G;
   const unsigned gmask = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
   const unsigned submask = gmask << subshift;
   const int n = p.n;
-  const int nblocks = gridDim.x;
-  if (threadIdx.x == 0) s_bid = (int)atomicAdd(p.status + nblocks, 1u);
-  __syncthreads();
-  const int bid = s_bid;
+  // Blocks are dispatched in index order, so every block a waiter looks back
+  // at (lower index) is resident or finished; the wait below is bounded anyway.
+  const int bid = blockIdx.x;
+  uint32_t *const status0 = p.status;              // part0[b] published
+  uint32_t *const status1 = p.status + gridDim.x;  // part1[b] published
   const int i0 = (bid * S + s) * kChunk;
   const int cnt = n - i0 < kChunk ? n - i0 : kChunk;  // positions in this chunk (<= 0: none)
   const int D = p.D;
@@ -413,6 +416,11 @@ reduce_kernel(const __grid_constant__ BwdParams p) {
         cont = s_flags[s2] & kLeadCont;
       }
       cols.st(p.part0 + (int64_t)bid * D, a);
+      if (VEC || d0 + 128 >= D) {  // whole row written: publish it
+        __threadfence();
+        __syncwarp(submask);
+        if (gl == 0) st_relaxed_gpu(status0 + bid, 1u);
+      }
     }
     if (flags & kHasTrail) {
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -422,18 +430,19 @@ reduce_kernel(const __grid_constant__ BwdParams p) {
         add4(a, s_lead[s2][gl]);
         cont = s_flags[s2] & kLeadCont;
       }
-      if (cont)  // leaves the block: the block in which it ends completes it
+      if (cont) {  // leaves the block: the block in which it ends completes it
         cols.st(p.part1 + (int64_t)bid * D, a);
-      else
+        if (VEC || d0 + 128 >= D) {
+          __threadfence();
+          __syncwarp(submask);
+          if (gl == 0) st_relaxed_gpu(status1 + bid, 1u);
+        }
+      } else {
         cols.st(wlast, sgd_row(p.lr, a, cols.ld(wlast)));
+      }
     }
     if (!VEC) __syncthreads();  // shared partials are reused by the next column tile
   }
-
-  // ---- publish this block's partials ----------------------------------------
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) st_release_gpu(p.status + bid, 1u);
 
   // ---- complete the chain that ends in this block ---------------------------
   if (s != 0 || !(s_flags[0] & kHasLead)) return;
@@ -465,7 +474,8 @@ reduce_kernel(const __grid_constant__ BwdParams p) {
   {
     const unsigned long long t0 = bwd_timer_ns();
     for (int j = c + gl; j < bid; j += G) {
-      while (ld_acquire_gpu(p.status + j) == 0u) {
+      const uint32_t *flag = j == c ? status1 + j : status0 + j;
+      while (ld_acquire_gpu(flag) == 0u) {
         if (bwd_timer_ns() - t0 > 2000000000ull) {  // 2 s: a lower ticket never published
           if (p.err) *p.err = FFEMB_ERR_CUDA;
           break;
@@ -528,7 +538,7 @@ struct Workspace {
   void *sort_tmp;
   size_t sort_tmp_bytes;
   float *part0, *part1;
-  uint32_t *status;  // [blocks + 1]: per-block "published" words, then the ticket counter
+  uint32_t *status;  // [2][blocks]: "part0 published", "part1 published"
   size_t status_bytes;
   size_t total;
 };
@@ -565,16 +575,18 @@ static Workspace carve(void *base, int64_t n, int64_t total_entries, int D) {
     off += align256(bytes);
     return q;
   };
+  // keys_a and vals_a are adjacent: the on-chip sort uses the pair as one
+  // array of n 8-byte (row, bag) records between its passes
   w.keys_a = take(n * w.key_bytes);
-  w.keys_b = take(n * w.key_bytes);
   w.vals_a = (uint32_t *)take(n * 4);
+  w.keys_b = take(n * w.key_bytes);
   w.vals_b = (uint32_t *)take(n * 4);
   w.sort_tmp_bytes = sort_tmp_bytes(n, wide);
   if (!wide && own_sort_hist_bytes(n) > w.sort_tmp_bytes) w.sort_tmp_bytes = own_sort_hist_bytes(n);
   w.sort_tmp = take(w.sort_tmp_bytes);
   w.part0 = (float *)take((size_t)blocks * D * 4);
   w.part1 = (float *)take((size_t)blocks * D * 4);
-  w.status_bytes = (size_t)(blocks + 1) * sizeof(uint32_t);
+  w.status_bytes = (size_t)blocks * 2 * sizeof(uint32_t);
   w.status = (uint32_t *)take(w.status_bytes);
   w.total = off;
   return w;
@@ -619,7 +631,15 @@ static Group group_of(const ffemb_lookup_t *lookups, int T) {
 template <typename KeyT>
 static int sort_group(const ffemb_lookup_t *lookups, int T, int batch, const Workspace &w,
                       const Group &g, int *err, cudaStream_t s) {
-  if (sizeof(KeyT) == 4 && g_sort_impl.load(std::memory_order_relaxed) == 1)
+  const int impl = g_sort_impl.load(std::memory_order_relaxed);
+  if (sizeof(KeyT) == 4 && impl == 2) {
+    bool done = false;
+    if (int rc = cluster_sort_group(lookups, T, batch, (uint32_t *)w.keys_b, w.vals_b, (uint2 *)w.keys_a,
+                                    err, s, &done))
+      return rc;
+    if (done) return FFEMB_OK;
+  }
+  if (sizeof(KeyT) == 4 && impl >= 1)
     return own_sort_group(lookups, T, batch, (uint32_t *)w.keys_a, (uint32_t *)w.keys_b, w.vals_a,
                           w.vals_b, (uint32_t *)w.sort_tmp, err, s);
   KeyParams kp;
@@ -679,7 +699,7 @@ static int update_group(const ffemb_lookup_t *lookups, int T, int batch, int out
   bp.D = out_dim;
   bp.avg = avg;
   bp.lr = lr;
-  // every block's "published" word and the ticket counter start from zero
+  // every block's "published" words start from zero
   FFEMB_CUDA_OK(cudaMemsetAsync(w.status, 0, w.status_bytes, s));
   if (wide_keys(g.total_entries))
     launch_reduce_g<uint64_t>(bp, vec, s);
@@ -737,7 +757,8 @@ static int backward_impl(int phases, const ffemb_lookup_t *lookups, int num_tabl
 using namespace ffemb;
 
 extern "C" int ffemb_set_sort_impl(int impl) {
-  if (impl != 0 && impl != 1) return fail(FFEMB_ERR_INVALID_ARGUMENT, "set_sort_impl: 0 (library) or 1 (own)");
+  if (impl < 0 || impl > 2)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "set_sort_impl: 0 (library), 1 (own, global passes) or 2 (own, on-chip)");
   g_sort_impl.store(impl);
   return FFEMB_OK;
 }
@@ -802,8 +823,8 @@ extern "C" int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tab
 //     make that first call outside any stream capture;
 //   * all calls on one device share the one array.  It still holds whatever
 //     the previous call left there; the only part that has to start from
-//     zero -- the blocks' "published" words and the ticket counter of the
-//     reduce kernel -- is cleared by every call on its stream before use.
+//     zero -- the blocks' "published" words of the reduce kernel -- is
+//     cleared by every call on its stream before use.
 //     Two calls that overlap on the GPU (different streams, or different host
 //     threads) would trample each other's keys and partial sums: serialise
 //     them.

@@ -35,7 +35,10 @@ struct FwdParams {
 };
 
 constexpr int kFwdThreads = 256;
-constexpr int kUnroll = 8;  // independent row loads in flight per lane
+#ifndef FFEMB_FWD_UNROLL
+#define FFEMB_FWD_UNROLL 8
+#endif
+constexpr int kUnroll = FFEMB_FWD_UNROLL;  // independent row loads in flight per lane
 
 // ---------------------------------------------------------------------------
 // One-hot (bag size 1): a warp owns 32 consecutive bags of one table.  Lane i

@@ -142,12 +142,18 @@ int ffemb_embed_backward_sgd(const ffemb_lookup_t *lookups, int num_tables,
                              void *workspace, size_t workspace_bytes,
                              int *err_flag, void *stream);
 
-/* Which key sort the backward uses (process-wide).  0: the CUDA toolkit's
- * DeviceRadixSort over the global (table,row) keys; 1: this library's own
- * segmented sort (csrc/ffemb_sort.cuh), which sorts every table's segment by
- * row number with only as many passes as that table's size needs.  Both are
- * stable, so they produce the same order and bit-identical results.  Launch
- * groups whose tables hold 2^32-1 rows or more always use 0. */
+/* Which key sort the backward uses (process-wide).
+ *   2 (default): this library's one-launch on-chip sort (csrc/ffemb_csort.cuh):
+ *      one thread-block cluster per table keeps the table's whole segment in
+ *      distributed shared memory across its radix passes.  Used when every
+ *      table of the launch has at most 65536 lookups and batch <= 65536;
+ *      otherwise 1 is used.
+ *   1: this library's segmented sort through global memory
+ *      (csrc/ffemb_sort.cuh), every table's segment sorted by row number with
+ *      only as many passes as that table's size needs.
+ *   0: the CUDA toolkit's DeviceRadixSort over the global (table,row) keys.
+ * All are stable, so they produce the same order and bit-identical results.
+ * Launch groups whose tables hold 2^32-1 rows or more always use 0. */
 int ffemb_set_sort_impl(int impl);
 int ffemb_get_sort_impl(void);
 
@@ -183,9 +189,8 @@ int ffemb_embed_sgd_update(const ffemb_lookup_t *lookups, int num_tables,
  *     (two host threads may make it at the same time); make that call before
  *     any stream capture begins.
  *   - All calls on a device share the array and find the previous call's
- *     data in it; the reduce kernel's per-block status words and its ticket
- *     counter, the only part that must start at zero, are cleared by each
- *     call.  Calls that overlap on the GPU race on the
+ *     data in it; the reduce kernel's per-block status words, the only part
+ *     that must start at zero, are cleared by each call.  Calls that overlap on the GPU race on the
  *     array: issue them one after the other on one stream.
  * Inputs, outputs and results are those of ffemb_embed_backward_sgd. */
 size_t ffemb_static_scratch_bytes(void);

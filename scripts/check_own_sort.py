@@ -43,7 +43,12 @@ def main():
         g = torch.randn(B, len(rows) * D, device="cuda", generator=gen)
         a, ea = step(0, Ws, idxs, g, aggr)
         b, eb = step(1, Ws, idxs, g, aggr)
-        same = all(torch.equal(x, y) for x, y in zip(a, b)) and ea == eb == 3
+        c, ec = step(2, Ws, idxs, g, aggr)
+        # an out-of-range index sits at the end of its TABLE's segment for the own sorts and at the
+        # end of the whole array for the library sort: later tables shift against the 32-position
+        # chunks, so 0 vs own is within 1e-5, own vs own is bit-identical
+        close = all(torch.allclose(x, y, rtol=1e-5, atol=1e-5) for x, y in zip(a, b))
+        same = close and all(torch.equal(y, z) for y, z in zip(b, c)) and ea == eb == ec == 3
         changed = any(not torch.equal(x, w) for x, w in zip(a, Ws))
         print("case rows=%s.. D=%d B=%d L=%d: %s" % (rows[:4], D, B, L, "ok" if same and changed else "MISMATCH"))
         ok = ok and same and changed
@@ -65,7 +70,7 @@ def main():
     idxs = [workloads.gen_indices(torch, n, B, 1, "uniform", 0.0, gen) for n in rows]
     ws = K.alloc_workspace(len(rows) * B, sum(rows), D)
     lk = K.make_lookups(Ws, idxs)
-    for impl in (0, 1):
+    for impl in (0, 1, 2):
         K.set_sort_impl(impl)
         for _ in range(3):
             K.embed_backward_sort(lk, B, D, ws)
@@ -76,8 +81,8 @@ def main():
             K.embed_backward_sort(lk, B, D, ws)
         e.record()
         torch.cuda.synchronize()
-        print("C3 sort phase, impl %d: %.1f us" % (impl, s.elapsed_time(e) / 50 * 1e3))
-    K.set_sort_impl(0)
+        print("C3 sort phase, impl %d: %.1f us" % (impl, s.elapsed_time(e) / 30 * 1e3))
+    K.set_sort_impl(2)
     print("ALL OK" if ok else "FAILED")
     return 0 if ok else 1
 
