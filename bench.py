@@ -288,7 +288,7 @@ def run_ours(args, w):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    if world > 1:
+    if world > 1 and args.exchange == "nccl":
         return run_sharded(args, w, rank, world, local_rank)
 
     D, B, L, aggr = w["dim"], w["batch"], w["bag"], w["aggr"]
@@ -296,11 +296,25 @@ def run_ours(args, w):
     T = len(rows)
     stream = torch.cuda.current_stream()
 
+    # The same ff.embedding program on every rank; with more than
+    # one rank the library places the tables and does both exchanges.
     cfg = ff.FFConfig()
     cfg.set_batch_size(B)
-    cfg.set_rank(0, local_rank)
+    cfg.set_workers_per_node(world)
+    cfg.set_rank(rank, local_rank)
+    if world > 1:
+        cfg.set_replicate_below({"auto": -1, "off": 0}.get(args.replicate, args.replicate))
     m = ff.FFModel(cfg)
     m.set_stream(stream.cuda_stream)
+    if world > 1 and args.placement == "balance":
+        below = {"auto": B // world, "off": 0}.get(args.replicate, args.replicate)
+        below = int(below)
+        sharded_t = [t for t in range(T) if rows[t] >= below]
+        owners = ff.balance_placement([rows[t] for t in sharded_t], [B * L] * len(sharded_t), D, world, 150 << 30)
+        st = ff.Strategy()
+        for t, o in zip(sharded_t, owners):
+            st.add_op("embedding%d" % t, 0, [1, 1], [o])
+        m.set_strategy(st)
     ins, outs = [], []
     for t in range(T):
         x = m.create_tensor([B, L], ff.DataType.DT_INT64)
@@ -309,27 +323,36 @@ def run_ours(args, w):
         ins.append(x)
     m.compile(optimizer=ff.SGDOptimizer(m, args.lr))
     m.init_layers()
+    owner = [m.get_layer_by_id(t).get_device() for t in range(T)]      # -1: replicated on every rank
+    held = [t for t in range(T) if owner[t] in (rank, -1)]              # tables whose indices this rank reads
+    Bs = B // world
 
     gen = torch.Generator(device="cuda")
-    gen.manual_seed(4321)
-    pool = torch.empty((args.pool, T, B, L), dtype=torch.int64, device="cuda")
+    gen.manual_seed(4321 + rank)
+    # index tensors are [B, L] for every table; a rank fills those it reads
+    pool = torch.zeros((args.pool, len(held), B, L), dtype=torch.int64, device="cuda")
     for p in range(args.pool):
+        for i, t in enumerate(held):
+            pool[p, i] = workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen)
+    if world == 1:
+        out = torch.empty((B, T * D), device="cuda")
+        grad = torch.randn((B, T * D), device="cuda", generator=gen)
         for t in range(T):
-            pool[p, t] = workloads.gen_indices(torch, rows[t], B, L, args.dist, args.alpha, gen)
-    out = torch.empty((B, T * D), device="cuda")
-    grad = torch.randn((B, T * D), device="cuda", generator=gen)
-    for t in range(T):
-        outs[t].attach_torch(out[:, t * D:(t + 1) * D])
-        outs[t].attach_torch(grad[:, t * D:(t + 1) * D], grad=True)
+            outs[t].attach_torch(out[:, t * D:(t + 1) * D])
+            outs[t].attach_torch(grad[:, t * D:(t + 1) * D], grad=True)
+    else:       # this rank's [B/N, T*D] slices live in the library's peer-mapped exchange buffer
+        out, grad = m.exchange_matrix(False), m.exchange_matrix(True)
+        grad.normal_(generator=gen)
     n_lookups = T * B * L
+    n_mine = sum(B if owner[t] == rank else Bs for t in held) * L       # lookups this rank's kernels process
 
     flush = None
     if w["working_set"] <= 2 * 126e6:
         flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def step(p, ev=None):
-        for t in range(T):
-            ins[t].attach_torch(pool[p, t])
+        for i, t in enumerate(held):
+            ins[t].attach_torch(pool[p, i])
         if ev:
             ev[0].record()
         m.forward()
@@ -344,12 +367,13 @@ def run_ours(args, w):
             ev[3].record()
 
     launches_per_step = None
+    g_fwd = g_bwd = None
     if args.graph:
         # The step as two CUDA graphs (forward | backward + update) over a fixed
         # index buffer: the per-step host work is one small copy and two replays.
         idx_static = torch.empty_like(pool[0])
-        for t in range(T):
-            ins[t].attach_torch(idx_static[t])
+        for i, t in enumerate(held):
+            ins[t].attach_torch(idx_static[i])
         idx_static.copy_(pool[0])
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
@@ -359,6 +383,8 @@ def run_ours(args, w):
                 m.forward(); m.zero_gradients(); m.backward(); m.update()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
         l0 = kernels.kernel_launch_count()
         g_fwd, g_bwd = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         with torch.cuda.graph(g_fwd):
@@ -395,152 +421,200 @@ def run_ours(args, w):
     sampler = ClockSampler(local_rank)
     sampler.start()
     launches0 = kernels.kernel_launch_count()
+    if dist is not None:
+        dist.barrier()
     torch.cuda.synchronize()
     for i in range(K):
         step((args.warmup + i) % args.pool, evs[i])
         if flush is not None:
             flush.zero_()
     torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
     launches = kernels.kernel_launch_count() - launches0
     if launches_per_step is not None:
         launches = launches_per_step * K      # replayed from the captured graphs
     clocks = sampler.stop()
-    m.sync()   # surfaces an out-of-range index as an error
+    m.sync()   # surfaces an out-of-range index (or a barrier time-out) as an error
 
     if flush is None:
         total_ms = evs[0][0].elapsed_time(evs[-1][3])
     else:
         total_ms = sum(e[0].elapsed_time(e[3]) for e in evs)
-    ms_step = total_ms / K
     fwd_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / K
     sort_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / K
     upd_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / K
+    ms_step = total_ms / K
+    if dist is not None:        # device time, max over ranks
+        tt = torch.tensor([ms_step, fwd_ms, sort_ms, upd_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_step, fwd_ms, sort_ms, upd_ms = tt.tolist()
     # unique (table,row) pairs per batch = the rows the update reads and writes
     # (counted after the timed region so that no library sort shows up in profiles)
-    uniq = []
-    for p in range(args.pool):
-        uniq.append(sum(int(torch.unique(pool[p, t]).numel()) for t in range(T)))
+    used = sorted(set((args.warmup + i) % args.pool for i in range(K)))
+    uniq = {}
+    for p in used:
+        u = 0
+        for i, t in enumerate(held):
+            if owner[t] == rank:
+                u += int(torch.unique(pool[p, i]).numel())
+            else:       # replicated: rows touched by any rank's samples
+                mask = torch.zeros(rows[t], device="cuda")
+                mask[pool[p, i, rank * Bs:(rank + 1) * Bs].reshape(-1)] = 1.0
+                dist.all_reduce(mask, op=dist.ReduceOp.MAX)
+                if rank == 0:
+                    u += int(mask.sum().item())
+        uniq[p] = u
     U = sum(uniq[(args.warmup + i) % args.pool] for i in range(K)) / K
+    my_U = U
+    if dist is not None:
+        ut = torch.tensor([U], device="cuda", dtype=torch.float64)
+        dist.all_reduce(ut)
+        U = float(ut.item())
 
     peak, peak_src = measured_peaks()
     fwd_bytes = n_lookups * D * 4                  # rows gathered
     upd_bytes = 2 * U * D * 4                      # touched rows read + written
     step_bytes = fwd_bytes + upd_bytes
-    phases = {
-        "forward": {"ms": fwd_ms, "algorithmic_bytes": fwd_bytes, "gbs": fwd_bytes / fwd_ms / 1e6,
-                    "full_bytes": fwd_bytes * 2 + n_lookups * 8},
-        "backward_sort": {"ms": sort_ms, "algorithmic_bytes": 0, "keys": n_lookups},
-        "sgd_update": {"ms": upd_ms, "algorithmic_bytes": upd_bytes, "gbs": upd_bytes / upd_ms / 1e6,
-                       "full_bytes": upd_bytes + n_lookups * D * 4 + n_lookups * 8},
-    }
-    dom = "sgd_update" if upd_ms >= fwd_ms else "forward"
-    traffic = None
-    try:   # DRAM bytes per launch of that kernel from the committed ncu capture of this workload
-        if args.dist == "uniform":
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[w["name"]][dom]
-    except Exception:
-        traffic = None
-    roofline = {"bound": "hbm",
-                "kernel": "reduce_l1_kernel (segment reduce + sparse SGD; timed with its l2/l3 tails)"
-                if dom == "sgd_update" else "fwd_onehot/multihot_kernel (gather-and-pool; timed with the "
-                "overlapped key sort's join)",
-                "achieved": phases[dom]["gbs"], "peak": peak, "unit": "GB/s",
-                "frac": phases[dom]["gbs"] / peak, "peak_source": peak_src, "traffic": traffic,
-                "achieved_full": phases[dom]["full_bytes"] / phases[dom]["ms"] / 1e6}
+    traffic, traffic_src = None, None
+    if world == 1:
+        phases = {
+            "forward": {"ms": fwd_ms, "algorithmic_bytes": fwd_bytes, "gbs": fwd_bytes / fwd_ms / 1e6,
+                        "full_bytes": fwd_bytes * 2 + n_lookups * 8},
+            "backward_sort": {"ms": sort_ms, "algorithmic_bytes": 0, "keys": n_lookups},
+            "sgd_update": {"ms": upd_ms, "algorithmic_bytes": upd_bytes, "gbs": upd_bytes / upd_ms / 1e6,
+                           "full_bytes": upd_bytes + n_lookups * D * 4 + n_lookups * 8},
+        }
+        dom = "sgd_update" if upd_ms >= fwd_ms else "forward"
+        try:   # DRAM bytes per launch of that kernel: from the committed ncu capture, not from this run
+            if args.dist == "uniform":
+                tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+                traffic, traffic_src = tj[w["name"]][dom], tj.get("source")
+        except Exception:
+            traffic = None
+        roofline = {"bound": "hbm",
+                    "kernel": "reduce_kernel (segment reduce + sparse SGD, chains completed in the same launch)"
+                    if dom == "sgd_update" else "fwd_onehot/multihot_kernel (gather-and-pool; timed with the "
+                    "overlapped key sort's join)",
+                    "achieved": phases[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": phases[dom]["gbs"] / peak, "peak_source": peak_src, "traffic": traffic,
+                    "traffic_source": traffic_src,
+                    "achieved_full": phases[dom]["full_bytes"] / phases[dom]["ms"] / 1e6}
+    else:
+        # bytes this rank's own kernels move for its share of the step (its sharded
+        # tables' whole batch + its samples of the replicated tables)
+        my_bytes = n_mine * D * 4 + 2 * my_U * D * 4
+        phases = {"forward_and_exchange": {"ms": fwd_ms}, "gradient_exchange": {"ms": sort_ms},
+                  "update": {"ms": upd_ms}}
+        roofline = {"bound": "hbm", "kernel": "whole step on rank 0 (gather + sort + update + both exchanges)",
+                    "achieved": my_bytes / ms_step / 1e6, "peak": peak, "unit": "GB/s",
+                    "frac": my_bytes / ms_step / 1e6 / peak, "peak_source": peak_src, "traffic": None,
+                    "traffic_source": "not captured: ncu is never wrapped round a multi-rank run"}
     line = {
         "metric": METRIC, "value": B / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, w, world),
         "roofline": roofline,
         "step_roofline": {"algorithmic_bytes": step_bytes, "unique_rows": U, "lookups": n_lookups,
-                          "gbs": step_bytes / ms_step / 1e6, "frac_of_measured_peak": step_bytes / ms_step / 1e6 / peak,
-                          "frac_of_8tbs_nominal": step_bytes / ms_step / 1e6 / 8000.0},
+                          "gbs": step_bytes / ms_step / 1e6,
+                          "frac_of_measured_peak": step_bytes / ms_step / 1e6 / (peak * world),
+                          "frac_of_8tbs_nominal": step_bytes / ms_step / 1e6 / (8000.0 * world)},
         "phases": phases, "clocks": clocks, "gpu_launches": int(launches),
     }
+    if world > 1:
+        n_sh = [sum(1 for t in range(T) if owner[t] == r) for r in range(world)]
+        sent = max(n_sh) * B * D * 4 * (world - 1) // world      # bytes the busiest rank stores to its peers
+        line["exchange"] = {"mode": "p2p: forward stores and gradient pushes over peer memory, peer-memory barriers",
+                            "bytes_per_gpu_per_direction": sent,
+                            "forward_bus_gbs_lower_bound": sent / fwd_ms / 1e6,
+                            "gradient_bus_gbs_lower_bound": sent / max(sort_ms, 1e-9) / 1e6,
+                            "nvlink_gbs": {"nominal": 900.0, "measured_peer_copy": 770.0},
+                            "sharded_tables_per_rank": n_sh, "replicated_tables": sum(1 for o in owner if o < 0),
+                            "replicate_below_rows": (B // world) if args.replicate == "auto" else args.replicate,
+                            "replica_bytes": sum(rows[t] for t in range(T) if owner[t] < 0) * D * 4,
+                            "imbalance_bound": (T - sum(1 for o in owner if o < 0)) / float(world * max(max(n_sh), 1))}
+        line["config"]["placement"] = args.placement
     with _Guard(line, "step_ms_percentiles"):      # spread of the individual steps
         per = sorted(e[0].elapsed_time(e[3]) for e in evs)
         line["step_ms_percentiles"] = {"p10": per[len(per) // 10], "p50": per[len(per) // 2],
-                                       "p90": per[(len(per) * 9) // 10], "n": len(per)}
+                                       "p90": per[(len(per) * 9) // 10], "n": len(per), "rank": rank}
 
     # ---- end to end: host buffers in, host buffers out, through the public API.
     # Every step copies its indices and upstream gradients from pinned host memory
-    # and its pooled outputs back.  The device-side staging is double-buffered and
-    # the copies run on their own streams, so step i's compute overlaps the H2D of
-    # step i+1 and the D2H of step i-1 (PCIe is full duplex); the host picks up
-    # the result of step i-1 before it issues step i+1.
+    # and its pooled outputs back, through the library's double-buffered host
+    # pipeline (ffemb_model_load_batch_async / begin_batch / fetch_outputs_async):
+    # step i's kernels overlap the H2D of step i+1 and the D2H of step i-1 (PCIe
+    # is full duplex); the host picks up step i-1's result before it issues i+1.
+    # With N ranks every rank moves its own samples' slice over its own PCIe link.
     if not args.no_e2e:
         with _Guard(line, "e2e"):
             m.set_stream(stream.cuda_stream)
-            idx_host = pool[0].cpu().pin_memory()
-            grad_host = torch.empty((B, T * D), pin_memory=True)
-            grad_host.copy_(grad)
-            out_host = torch.empty((B, T * D), pin_memory=True)
-            NB = 2
-            idx_dev = [torch.empty_like(pool[0]) for _ in range(NB)]
-            out_dev = [out, torch.empty_like(out)]
-            grad_dev = [grad, torch.empty_like(grad)]
-            s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-            in_ev = [torch.cuda.Event() for _ in range(NB)]
-            fwd_ev = [torch.cuda.Event() for _ in range(NB)]
-            d2h_ev = [torch.cuda.Event() for _ in range(NB)]
-            done_ev = [torch.cuda.Event() for _ in range(NB)]
-            issued = [False] * NB
+            rows_here = B // world
+            idx_host = [None] * T
+            for i, t in enumerate(held):
+                idx_host[t] = pool[0, i].cpu().pin_memory()
+            grad_host = torch.empty((rows_here, T * D), pin_memory=True)
+            grad_host.copy_(grad[:, :T * D])
+            out_host = torch.empty((rows_here, T * D), pin_memory=True)
+            m.load_batch_async(idx_host, grad_host)
 
-            def e2e_step(i):
-                b = i % NB
-                with torch.cuda.stream(s_in):
-                    if issued[b]:
-                        s_in.wait_event(done_ev[b])          # step i-2 no longer reads these buffers
-                    idx_dev[b].copy_(idx_host, non_blocking=True)
-                    grad_dev[b].copy_(grad_host, non_blocking=True)
-                    in_ev[b].record(s_in)
-                stream.wait_event(in_ev[b])
-                if issued[b]:
-                    stream.wait_event(d2h_ev[b])             # step i-2's outputs have left out_dev[b]
-                for t in range(T):
-                    ins[t].attach_torch(idx_dev[b][t])
-                    outs[t].attach_torch(out_dev[b][:, t * D:(t + 1) * D])
-                    outs[t].attach_torch(grad_dev[b][:, t * D:(t + 1) * D], grad=True)
+            def e2e_step():
+                m.begin_batch()
                 m.forward()
-                fwd_ev[b].record(stream)
-                with torch.cuda.stream(s_out):
-                    s_out.wait_event(fwd_ev[b])
-                    out_host.copy_(out_dev[b], non_blocking=True)
-                    d2h_ev[b].record(s_out)
+                m.fetch_outputs_async(out_host)
                 m.zero_gradients()
                 m.backward()
                 m.update()
-                done_ev[b].record(stream)
-                issued[b] = True
-                if i > 0:
-                    d2h_ev[(i - 1) % NB].synchronize()       # the host now owns step i-1's pooled output
+                m.load_batch_async(idx_host, grad_host)      # the next batch, under this one's kernels
+                m.wait_outputs()                             # the host now owns the previous step's pooled output
 
-            for i in range(NB):
-                e2e_step(i)
+            for _ in range(2):
+                e2e_step()
+            m.wait_outputs(all=True)
             torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
-            for i in range(args.e2e_steps):
-                e2e_step(NB + i)
-            s_out.synchronize()
-            stream.wait_stream(s_out)
-            stream.wait_stream(s_in)
+            for _ in range(args.e2e_steps):
+                e2e_step()
+            m.wait_outputs(all=True)
+            torch.cuda.synchronize()                         # the last prefetch has landed too
             e.record()
             torch.cuda.synchronize()
             e2e_ms = s.elapsed_time(e) / args.e2e_steps
+            if dist is not None:
+                tt = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                e2e_ms = float(tt.item())
+            h2d = sum(B * L * 8 if owner[t] == rank else rows_here * L * 8 for t in held) + grad_host.numel() * 4
             line["e2e"] = {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
-                           "h2d_bytes_per_step": idx_host.numel() * 8 + grad_host.numel() * 4,
-                           "d2h_bytes_per_step": out_host.numel() * 4, "steps": args.e2e_steps,
-                           "pipelining": "double-buffered: H2D of step i+1 and D2H of step i-1 overlap step i"}
+                           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": out_host.numel() * 4,
+                           "steps": args.e2e_steps, "api": "ffemb_model_load_batch_async / begin_batch / "
+                           "fetch_outputs_async / wait_outputs",
+                           "pipelining": "double-buffered: H2D of step i+1 and D2H of step i-1 overlap step i",
+                           "note": "bytes are per rank; every rank copies its own samples' slice" if world > 1
+                           else "one GPU moves the whole batch"}
             m.sync()
-            del idx_host, grad_host, out_host, idx_dev, out_dev, grad_dev
+            del idx_host, grad_host, out_host
 
-    if not args.no_cpu_baseline and rank == 0 and world == 1:
+    if not args.no_cpu_baseline and rank == 0:
         with _Guard(line, "cpu_baseline"):
             cb = cpu_reference_run(w, args.cpu_steps, 1, args.cpu_row_cap, args.lr)
             line["cpu_baseline"] = {k: cb[k] for k in CPU_KEYS}
     if rank == 0:
         emit(line)
+    if dist is not None:
+        dist.barrier()      # rank 0 may have spent a while on the CPU baseline
+        # Teardown order matters: captured graphs first, then the peer mappings
+        # (every rank past its last kernel), then the process group.
+        _arm_exit_watchdog(60.0)
+        g_fwd = g_bwd = None      # noqa: F841
+        torch.cuda.synchronize()
+        dist.barrier()
+        m.close()
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def run_sharded(args, w, rank, world, local_rank):

@@ -83,6 +83,7 @@ SIGNATURES = {
     "ffemb_ipc_close_handle": (_i, [_vp]),
     "ffemb_peer_barrier": (_i, [C.POINTER(C.c_void_p), _i, _i, _vp, _vp]),
     "ffemb_push_columns": (_i, [C.POINTER(Push), _i, _i, _i, _vp, _i64, _vp]),
+    "ffemb_replica_reduce_update": (_i, [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i64, _i, _i, _f, _vp]),
     # config
     "ffemb_config_create": (_H, []),
     "ffemb_config_destroy": (None, [_H]),
@@ -95,6 +96,8 @@ SIGNATURES = {
     "ffemb_config_set_rank": (_i, [_H, _i, _i]),
     "ffemb_config_get_rank": (_i, [_H]),
     "ffemb_config_import_strategy_file": (_i, [_H, _cp]),
+    "ffemb_config_set_replicate_below": (_i, [_H, _i64]),
+    "ffemb_config_set_exchange_engine": (_i, [_H, _i]),
     # model
     "ffemb_model_create": (_H, [_H]),
     "ffemb_model_destroy": (None, [_H]),
@@ -116,6 +119,14 @@ SIGNATURES = {
     "ffemb_model_get_num_layers": (_i, [_H]),
     "ffemb_model_get_layer_by_id": (_H, [_H, _i]),
     "ffemb_model_set_strategy": (_i, [_H, _H]),
+    "ffemb_model_is_sharded": (_i, [_H]),
+    "ffemb_model_get_exchange_handle": (_i, [_H, _vp]),
+    "ffemb_model_connect_peers": (_i, [_H, _vp, _i]),
+    "ffemb_model_get_exchange_matrix": (_i, [_H, _b, C.POINTER(C.c_void_p), C.POINTER(_i64), _ip]),
+    "ffemb_model_load_batch_async": (_i, [_H, C.POINTER(C.c_void_p), _vp]),
+    "ffemb_model_begin_batch": (_i, [_H]),
+    "ffemb_model_fetch_outputs_async": (_i, [_H, _vp]),
+    "ffemb_model_wait_outputs": (_i, [_H, _b]),
     # op
     "ffemb_op_get_parameter_by_id": (_H, [_H, _i]),
     "ffemb_op_get_input_by_id": (_H, [_H, _i]),

@@ -98,6 +98,8 @@ class FFConfig(_Owned):
                 check(lib().ffemb_config_set_num_nodes(self.handle, int(argv[i + 1]))); i += 1
             elif a in ("--import", "--import-strategy") and i + 1 < len(argv):
                 self.import_strategy_file(argv[i + 1]); i += 1
+            elif a == "--replicate-below" and i + 1 < len(argv):
+                self.set_replicate_below(argv[i + 1] if argv[i + 1] == "auto" else int(argv[i + 1])); i += 1
             i += 1
 
     def get_batch_size(self):
@@ -126,6 +128,17 @@ class FFConfig(_Owned):
 
     def import_strategy_file(self, path):
         check(lib().ffemb_config_import_strategy_file(self.handle, path.encode()))
+
+    def set_replicate_below(self, rows):
+        """More than one rank: tables with fewer rows than this stay on every rank
+        (data-parallel, src/runtime/model.cc:697-724) instead of being sharded.
+        0: shard everything (the reference's strategy files); -1 or "auto":
+        batch / ranks, where a replica becomes cheaper than a shard."""
+        check(lib().ffemb_config_set_replicate_below(self.handle, -1 if rows == "auto" else int(rows)))
+
+    def set_exchange_engine(self, force=True):
+        """Run the sharded engine even with one rank (single-GPU tests)."""
+        check(lib().ffemb_config_set_exchange_engine(self.handle, int(bool(force))))
 
     def begin_trace(self, trace_id):
         """Legion tracing (flexflow_begin_trace) has no counterpart: steps are
@@ -173,6 +186,13 @@ class Tensor(object):
     def get_array(self, ffmodel, data_type=None):
         """Device -> host copy of an embedding output (blocks)."""
         out = np.empty(self.dims, dtype=np.float32)
+        check(lib().ffemb_tensor_get_float(self.handle, ffmodel.handle, out.ctypes.data, out.size))
+        return out
+
+    def get_array_slice(self, ffmodel):
+        """Sharded mode: this rank's samples of an embedding output, [batch/ranks, out_dim] (blocks)."""
+        world = ffmodel._ffconfig.get_workers_per_node() * ffmodel._ffconfig.get_num_nodes()
+        out = np.empty((self.dims[0] // world, self.dims[1]), dtype=np.float32)
         check(lib().ffemb_tensor_get_float(self.handle, ffmodel.handle, out.ctypes.data, out.size))
         return out
 
@@ -439,12 +459,81 @@ class FFModel(_Owned):
     def set_stream(self, cuda_stream_ptr):
         check(lib().ffemb_model_set_stream(self.handle, cuda_stream_ptr))
 
-    def compile(self, optimizer=None, loss_type=None, metrics=None):
-        """loss_type / metrics belong to the dense part of the model and are ignored."""
+    def compile(self, optimizer=None, loss_type=None, metrics=None, group=None):
+        """loss_type / metrics belong to the dense part of the model and are ignored.
+
+        With more than one rank (FFConfig workers_per_node * num_nodes, one
+        process per GPU) the ranks' exchange buffers are connected here: the
+        64-byte IPC handles travel through torch.distributed (`group`, default
+        group if None), which must be initialised."""
         if optimizer is not None:
             assert isinstance(optimizer, SGDOptimizer), "unknow optimizer type (this path: SGD)"
             self.set_sgd_optimizer(optimizer)
         check(lib().ffemb_model_compile(self.handle))
+        world = self._ffconfig.get_workers_per_node() * self._ffconfig.get_num_nodes()
+        self._group = group
+        self._world = world
+        if world > 1:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                raise FFEmbError(_lib.FFEMB_ERR_COMM, "more than one rank: initialise torch.distributed "
+                                 "before FFModel.compile (it carries the ranks' IPC handles)")
+            mine = (C.c_uint8 * 64)()
+            check(lib().ffemb_model_get_exchange_handle(self.handle, mine))
+            handles = [None] * world
+            dist.all_gather_object(handles, bytes(mine), group=group)
+            buf = (C.c_uint8 * (64 * world)).from_buffer_copy(b"".join(handles))
+            check(lib().ffemb_model_connect_peers(self.handle, buf, world))
+            dist.barrier(group=group)      # every rank is connected before anyone stores into a peer
+
+    # -- double-buffered host ingest / egress (the reference: DataLoader::next_batch,
+    #    examples/cpp/DLRM/dlrm.cc:486-524, and zero-copy outputs, embedding.cu:280-284)
+    def load_batch_async(self, indices, out_grad=None):
+        """indices: per layer a pinned torch int64 [batch, bag] tensor (or None for a
+        table this rank does not read); out_grad: pinned torch float32 [rows, sum D]."""
+        n = len(indices)
+        arr = (C.c_void_p * n)(*[None if i is None else i.data_ptr() for i in indices])
+        self._pipe_keep = (indices, out_grad)
+        check(lib().ffemb_model_load_batch_async(self.handle, arr, None if out_grad is None else out_grad.data_ptr()))
+
+    def begin_batch(self):
+        check(lib().ffemb_model_begin_batch(self.handle))
+
+    def fetch_outputs_async(self, out_host):
+        self._pipe_out = out_host
+        check(lib().ffemb_model_fetch_outputs_async(self.handle, out_host.data_ptr()))
+
+    def wait_outputs(self, all=False):
+        check(lib().ffemb_model_wait_outputs(self.handle, bool(all)))
+
+    def is_sharded(self):
+        return bool(lib().ffemb_model_is_sharded(self.handle))
+
+    def exchange_matrix(self, grad=False):
+        """Sharded mode: zero-copy torch view of this rank's [batch/ranks, sum D]
+        output (or gradient) matrix, every table's block side by side."""
+        import torch
+        ptr, ld, rows = C.c_void_p(), C.c_int64(), C.c_int()
+        check(lib().ffemb_model_get_exchange_matrix(self.handle, grad, C.byref(ptr), C.byref(ld), C.byref(rows)))
+
+        class _Mem(object):
+            pass
+        holder = _Mem()
+        holder.__cuda_array_interface__ = {"shape": (rows.value, ld.value), "typestr": "<f4",
+                                           "data": (ptr.value, False), "version": 2, "strides": None}
+        return torch.as_tensor(holder, device="cuda")
+
+    def close(self):
+        """Sharded mode: no rank unmaps its peers' memory while one of them may
+        still be storing into it.  Collective; call it on every rank."""
+        if self.handle.impl:
+            if getattr(self, "_world", 1) > 1:
+                import torch
+                import torch.distributed as dist
+                torch.cuda.synchronize()
+                dist.barrier(group=self._group)
+            lib().ffemb_model_destroy(self.handle)
+            self.handle = _NULL
 
     def init_layers(self):
         check(lib().ffemb_model_init_layers(self.handle))

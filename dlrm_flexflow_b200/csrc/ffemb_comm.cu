@@ -224,3 +224,80 @@ extern "C" int ffemb_push_columns(const ffemb_push_t *items, int num_items, int 
   }
   return FFEMB_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Replicated small tables: sum of the gradient replicas fused with the SGD
+// step, over peer memory.  The reference sums the N gradient replicas of a
+// data-parallel embedding into replica 0 and runs the dense sgd_update
+// (src/runtime/optimizer_kernel.cu:96-106, src/runtime/model.cc:697-724).
+// Here every rank r owns the r-th slice of the replicated tables' flat
+// [count] array: it loads that slice of every rank's dense gradient through
+// the peer mappings (N loads in flight per lane), adds them in rank order,
+// applies W = fmaf(-lr, sum, W) once and stores the new slice into EVERY
+// rank's copy of the tables -- a reduce-scatter, the update and an all-gather
+// in one kernel, without a collective library and without a second pass over
+// the tables.  One rank computes each element, so the replicas stay bit
+// identical by construction.  The caller brackets it with two barriers: all
+// gradients complete before, all copies written after.
+// ---------------------------------------------------------------------------
+namespace ffemb {
+
+struct ReplicaParams {
+  float *W[kMaxParts];
+  const float *G[kMaxParts];
+  int64_t count4;  // float4 elements
+  int rank, world;
+  float lr;
+};
+
+__global__ void __launch_bounds__(256) replica_reduce_update_kernel(const __grid_constant__ ReplicaParams p) {
+  const int64_t per = (p.count4 + p.world - 1) / p.world;
+  const int64_t lo = per * p.rank;
+  const int64_t hi = lo + per < p.count4 ? lo + per : p.count4;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  for (int64_t i = lo + (int64_t)blockIdx.x * 256 + threadIdx.x; i < hi; i += stride) {
+    float4 g[kMaxParts];
+#pragma unroll
+    for (int q = 0; q < kMaxParts; ++q)
+      if (q < p.world) g[q] = __ldcg((const float4 *)p.G[q] + i);
+    float4 sum = g[0];  // replica 0 += replica q, q = 1.. (optimizer_kernel.cu:96-101)
+#pragma unroll
+    for (int q = 1; q < kMaxParts; ++q)
+      if (q < p.world) add4(sum, g[q]);
+    const float4 w = __ldcg((const float4 *)p.W[p.rank] + i);
+    const float4 nw = make_float4(fmaf(-p.lr, sum.x, w.x), fmaf(-p.lr, sum.y, w.y),
+                                  fmaf(-p.lr, sum.z, w.z), fmaf(-p.lr, sum.w, w.w));
+#pragma unroll
+    for (int q = 0; q < kMaxParts; ++q)
+      if (q < p.world) ((float4 *)p.W[q])[i] = nw;
+  }
+}
+
+}  // namespace ffemb
+
+extern "C" int ffemb_replica_reduce_update(float *const *weights, const float *const *grads,
+                                           int64_t count, int rank, int world, float lr,
+                                           void *stream) {
+  if (!weights || !grads || count < 0 || world < 1 || world > kMaxParts || rank < 0 || rank >= world)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "replica_reduce_update: bad arguments");
+  if (count % 4)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "replica_reduce_update: count must be a multiple of 4 floats");
+  if (count == 0) return FFEMB_OK;
+  ReplicaParams p;
+  for (int q = 0; q < kMaxParts; ++q) {
+    p.W[q] = q < world ? weights[q] : nullptr;
+    p.G[q] = q < world ? grads[q] : nullptr;
+    if (q < world && (!p.W[q] || !p.G[q] || ((uintptr_t)p.W[q] & 15) || ((uintptr_t)p.G[q] & 15)))
+      return fail(FFEMB_ERR_INVALID_ARGUMENT, "replica_reduce_update: NULL or unaligned replica pointer");
+  }
+  p.count4 = count / 4;
+  p.rank = rank;
+  p.world = world;
+  p.lr = lr;
+  const int64_t per = (p.count4 + world - 1) / world;
+  int64_t blocks = (per + 255) / 256;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  replica_reduce_update_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(p);
+  FFEMB_LAUNCH_OK("replica_reduce_update");
+  return FFEMB_OK;
+}

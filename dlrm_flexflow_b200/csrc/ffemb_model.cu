@@ -7,6 +7,7 @@
 // table (the placement hook), device buffers, one stream.
 #include <string.h>
 
+#include <algorithm>
 #include <memory>
 #include <vector>
 
@@ -24,6 +25,8 @@ struct Config {
   int rank = 0;
   int device = -1;            // -1: whatever device is current at model_create
   std::string strategy_file;
+  int64_t replicate_below = 0;  // world > 1: tables with fewer rows live on every rank; -1 = batch / world
+  int force_exchange = 0;       // run the sharded engine even with one rank (tests)
 };
 
 struct Initializer {
@@ -63,7 +66,11 @@ struct Op {
   int aggr;
   Initializer init;
   float *W = nullptr;
-  int owner = 0;
+  int owner = 0;            // rank that holds the table; -1: replicated on every rank
+  bool replicated = false;
+  float *G = nullptr;       // replicated: this rank's dense gradient replica
+  int64_t gcol = 0;         // sharded mode: first column in the [B/N][sum D] matrices
+  int64_t scol = 0;         // sharded mode: first column in the owner's staging matrix
   Parameter param;
 };
 
@@ -74,6 +81,30 @@ struct Sgd {
 };
 
 struct Strategy;  // ffemb_strategy.cc
+
+// Table-wise sharded mode (world > 1, one process per GPU): this rank's side
+// of the two exchanges.  One IPC-exportable allocation per rank,
+//   [ out B/N x ldx | 64 barrier words | grad B/N x ldx | replica W | replica G | staging B x stage_ld ]
+// whose first five parts have the same offsets on every rank.  Stands in for
+// what Legion DMA does for the reference at Concat (src/ops/concat.cu:85-93,
+// outputs in zero-copy memory: src/ops/embedding.cu:280-284,343-347).
+struct Exchange {
+  bool on = false, connected = false;
+  int Bs = 0;                 // samples per rank
+  int64_t ldx = 0;            // row stride of the out / grad matrices (all tables side by side)
+  std::vector<int64_t> stage_ld;  // per rank: row stride of its staging matrix
+  char *buf = nullptr;
+  size_t bytes = 0;
+  size_t off_out = 0, off_flags = 0, off_grad = 0, off_repW = 0, off_repG = 0, off_stage = 0;
+  char *peer[kMaxParts] = {};
+  int64_t rep_count = 0;      // floats in the flat replica arrays (multiple of 4)
+  int n_rep = 0, n_owned = 0;
+  void *rep_ws = nullptr;
+  size_t rep_ws_bytes = 0;
+  cudaStream_t rep_stream = nullptr;
+  cudaEvent_t ev_rep_fwd = nullptr, ev_rep_sorted = nullptr, ev_grads = nullptr, ev_rep_done = nullptr;
+  bool rep_pending = false;   // backward() left a replica gradient for update() to reduce
+};
 
 struct Model {
   Config cfg;
@@ -100,6 +131,8 @@ struct Model {
   float *out_mat = nullptr, *grad_mat = nullptr;  // library-owned [B][sum D] concat matrices
   int64_t mat_ld = 0;
   int op_guid = 100;  // Op guids start at 100 in the reference (model.cc:1165)
+  Exchange x;
+  struct HostPipe *pipe = nullptr;  // double-buffered host ingest / egress (below)
 };
 
 static Config *C(ffemb_config_t h) { return (Config *)h.impl; }
@@ -174,6 +207,9 @@ static int describe(const LaunchGroup &g, bool grad, std::vector<ffemb_lookup_t>
   return FFEMB_OK;
 }
 
+static void x_destroy(Model *m);     // sharded engine, below
+static void pipe_destroy(Model *m);  // host pipeline, below
+
 static void release(Buffer &b) {
   if (b.owned && b.ptr) cudaFree(b.ptr);
   b = Buffer();
@@ -211,6 +247,16 @@ extern "C" int ffemb_config_set_rank(ffemb_config_t h, int rank, int cuda_device
   return FFEMB_OK;
 }
 extern "C" int ffemb_config_get_rank(ffemb_config_t h) { return C(h) ? C(h)->rank : -1; }
+extern "C" int ffemb_config_set_replicate_below(ffemb_config_t h, int64_t rows) {
+  if (!C(h) || rows < -1) return fail(FFEMB_ERR_INVALID_ARGUMENT, "config_set_replicate_below: bad argument");
+  C(h)->replicate_below = rows;
+  return FFEMB_OK;
+}
+extern "C" int ffemb_config_set_exchange_engine(ffemb_config_t h, int force) {
+  if (!C(h)) return fail(FFEMB_ERR_INVALID_ARGUMENT, "config_set_exchange_engine: NULL config");
+  C(h)->force_exchange = force != 0;
+  return FFEMB_OK;
+}
 extern "C" int ffemb_config_import_strategy_file(ffemb_config_t h, const char *path) {
   if (!C(h) || !path) return fail(FFEMB_ERR_INVALID_ARGUMENT, "config_import_strategy_file: NULL argument");
   C(h)->strategy_file = path;
@@ -238,6 +284,8 @@ extern "C" void ffemb_model_destroy(ffemb_model_t h) {
   Model *m = M(h);
   if (!m) return;
   if (m->compiled) cudaSetDevice(m->device);
+  pipe_destroy(m);
+  x_destroy(m);
   for (auto &t : m->tensors) {
     release(t->data);
     release(t->grad);
@@ -378,6 +426,444 @@ extern "C" int ffemb_model_set_stream(ffemb_model_t h, void *stream) {
   return FFEMB_OK;
 }
 
+// ===========================================================================
+// Sharded engine (Exchange): forward / backward / update with world > 1.
+// ===========================================================================
+namespace ffemb {
+
+static size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// Launch groups of the sharded mode: this rank's sharded tables, or the
+// replicated ones, by (out_dim, aggr).
+struct XGroup {
+  int D, aggr;
+  std::vector<Op *> ops;
+};
+
+static std::vector<XGroup> x_groups(Model *m, bool rep) {
+  std::vector<XGroup> gs;
+  for (auto &up : m->ops) {
+    Op *op = up.get();
+    if (rep ? !op->replicated : (op->replicated || !owned(op))) continue;
+    XGroup *g = nullptr;
+    for (auto &c : gs)
+      if (c.D == op->D && c.aggr == op->aggr && (int)c.ops.size() < kMaxTables) g = &c;
+    if (!g) {
+      gs.push_back(XGroup{op->D, op->aggr, {}});
+      g = &gs.back();
+    }
+    g->ops.push_back(op);
+  }
+  return gs;
+}
+
+enum XMode { kXFwd, kXBwd, kXRepFwd, kXRepBwd };
+
+// lookups of one group.  Sharded tables see the whole batch; replicated ones
+// this rank's own samples, rows [rank*Bs, (rank+1)*Bs) of the index tensor.
+static int x_lookups(Model *m, const XGroup &g, XMode mode, std::vector<ffemb_lookup_t> &lk) {
+  const Exchange &x = m->x;
+  lk.clear();
+  for (Op *op : g.ops) {
+    if (!op->input->data.ptr)
+      return fail(FFEMB_ERR_INVALID_ARGUMENT, op->name + ": input tensor has no data");
+    const int L = op->input->dims[1];
+    ffemb_lookup_t l;
+    memset(&l, 0, sizeof l);
+    l.num_entries = op->N;
+    l.bag_size = L;
+    l.offsets = nullptr;
+    const int64_t *idx = (const int64_t *)op->input->data.ptr;
+    if (mode == kXFwd || mode == kXBwd) {
+      l.weight = op->W;
+      l.indices = idx;
+      l.num_indices = (int64_t)m->cfg.batch_size * L;
+      l.col = mode == kXFwd ? op->gcol : op->scol;
+    } else {
+      l.weight = mode == kXRepFwd ? op->W : op->G;
+      l.indices = idx + (int64_t)m->cfg.rank * x.Bs * L;
+      l.num_indices = (int64_t)x.Bs * L;
+      l.col = op->gcol;
+    }
+    lk.push_back(l);
+  }
+  return FFEMB_OK;
+}
+
+static ffemb_matrix_t x_matrix_out_peers(const Model *m) {  // forward: every rank's [Bs][ldx] out
+  ffemb_matrix_t mat;
+  memset(&mat, 0, sizeof mat);
+  for (int q = 0; q < m->world; ++q) mat.base[q] = (float *)(m->x.peer[q] + m->x.off_out);
+  mat.num_parts = m->world;
+  mat.rows_per_part = m->x.Bs;
+  mat.ld = m->x.ldx;
+  return mat;
+}
+
+static ffemb_matrix_t x_matrix_local(const Model *m, size_t off, int rows, int64_t ld) {
+  ffemb_matrix_t mat;
+  memset(&mat, 0, sizeof mat);
+  mat.base[0] = (float *)(m->x.buf + off);
+  mat.num_parts = 1;
+  mat.rows_per_part = rows;
+  mat.ld = ld;
+  return mat;
+}
+
+static int x_barrier(Model *m, int channel, cudaStream_t s) {
+  if (m->world <= 1) return FFEMB_OK;
+  uint32_t *flags[kMaxParts];
+  for (int q = 0; q < m->world; ++q) flags[q] = (uint32_t *)(m->x.peer[q] + m->x.off_flags) + 32 * channel;
+  return ffemb_peer_barrier(flags, m->cfg.rank, m->world, m->err_dev, s);
+}
+
+// sort and/or update over the groups of one kind; every group has its own
+// region of the workspace (sort results must survive until the update).
+static int x_backward_groups(Model *m, bool rep, bool sort, bool update, float lr, cudaStream_t s) {
+  const Exchange &x = m->x;
+  char *ws = (char *)(rep ? x.rep_ws : m->workspace);
+  const size_t ws_bytes = rep ? x.rep_ws_bytes : m->workspace_bytes;
+  const int batch = rep ? x.Bs : m->cfg.batch_size;
+  std::vector<ffemb_lookup_t> lk;
+  size_t off = 0;
+  for (const XGroup &g : x_groups(m, rep)) {
+    if (int rc = x_lookups(m, g, rep ? kXRepBwd : kXBwd, lk)) return rc;
+    int64_t n = 0, e = 0;
+    for (const ffemb_lookup_t &l : lk) {
+      n += l.num_indices;
+      e += l.num_entries;
+    }
+    const size_t need = up256(ffemb_embed_backward_workspace_bytes(n, e, g.D));
+    if (off + need > ws_bytes) return fail(FFEMB_ERR_WORKSPACE_TOO_SMALL, "backward: model workspace too small");
+    if (sort)
+      if (int rc = ffemb_embed_backward_sort(lk.data(), (int)lk.size(), batch, g.D, ws + off, need, m->err_dev, s))
+        return rc;
+    if (update) {
+      // replicas: dense gradient of this rank's own samples, from its [Bs][ldx]
+      // gradient matrix; sharded: the whole batch's gradient in the staging matrix
+      ffemb_matrix_t mat = rep ? x_matrix_local(m, x.off_grad, x.Bs, x.ldx)
+                               : x_matrix_local(m, x.off_stage, batch, x.stage_ld[m->cfg.rank]);
+      if (int rc = ffemb_embed_sgd_update(lk.data(), (int)lk.size(), batch, g.D, (enum AggrMode)g.aggr, &mat, lr,
+                                          ws + off, need, s))
+        return rc;
+    }
+    off += need;
+  }
+  return FFEMB_OK;
+}
+
+static std::vector<int64_t> x_signature(Model *m) {
+  std::vector<int64_t> sig;
+  for (auto &op : m->ops)
+    if (op->replicated || owned(op.get())) {
+      sig.push_back(op->index);
+      sig.push_back((int64_t)(uintptr_t)op->input->data.ptr);
+    }
+  return sig;
+}
+
+static int x_require_connected(Model *m, const char *who) {
+  if (!m->x.connected)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT,
+                std::string(who) + ": the ranks' exchange buffers are not connected yet "
+                                   "(ffemb_model_get_exchange_handle / ffemb_model_connect_peers)");
+  return FFEMB_OK;
+}
+
+static int x_forward(Model *m) {
+  Exchange &x = m->x;
+  if (int rc = x_require_connected(m, "forward")) return rc;
+  m->presorted = false;
+  const bool presort = m->presort && m->opt;
+  std::vector<ffemb_lookup_t> lk;
+  FFEMB_CUDA_OK(cudaEventRecord(m->ev_inputs, m->stream));
+  // The key sorts of the coming backward need only the indices: they go first,
+  // on their own streams, and run under the NVLink-bound gather.
+  if (presort && x.n_owned) {
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(m->side, m->ev_inputs, 0));
+    if (int rc = x_backward_groups(m, false, true, false, 0.f, m->side)) return rc;
+    FFEMB_CUDA_OK(cudaEventRecord(m->ev_sorted, m->side));
+  }
+  if (x.n_rep) {
+    // replicated tables: this rank's own samples, straight into its own slice;
+    // local traffic only, so it runs beside the sharded tables' gather
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(x.rep_stream, m->ev_inputs, 0));
+    ffemb_matrix_t own = x_matrix_local(m, x.off_out, x.Bs, x.ldx);
+    for (const XGroup &g : x_groups(m, true)) {
+      if (int rc = x_lookups(m, g, kXRepFwd, lk)) return rc;
+      if (int rc = ffemb_embed_forward(lk.data(), (int)lk.size(), x.Bs, g.D, (enum AggrMode)g.aggr, &own,
+                                       m->err_dev, x.rep_stream))
+        return rc;
+    }
+    FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_fwd, x.rep_stream));
+    if (presort) {
+      if (int rc = x_backward_groups(m, true, true, false, 0.f, x.rep_stream)) return rc;
+      FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_sorted, x.rep_stream));
+    }
+  }
+  // sharded tables: the whole batch, every pooled row stored straight into the
+  // consuming rank's [Bs][ldx] matrix over NVLink
+  if (x.n_owned) {
+    ffemb_matrix_t out = x_matrix_out_peers(m);
+    for (const XGroup &g : x_groups(m, false)) {
+      if (int rc = x_lookups(m, g, kXFwd, lk)) return rc;
+      if (int rc = ffemb_embed_forward(lk.data(), (int)lk.size(), m->cfg.batch_size, g.D, (enum AggrMode)g.aggr,
+                                       &out, m->err_dev, m->stream))
+        return rc;
+    }
+  }
+  if (int rc = x_barrier(m, 0, m->stream)) return rc;  // every rank's rows have landed
+  // join the forks: one timeline for the caller (and for a stream capture)
+  if (x.n_rep) {
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, x.ev_rep_fwd, 0));
+    if (presort) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, x.ev_rep_sorted, 0));
+  }
+  if (presort && x.n_owned) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, m->ev_sorted, 0));
+  if (presort) {
+    m->presort_sig = x_signature(m);
+    m->presorted = true;
+  }
+  return FFEMB_OK;
+}
+
+static int x_backward(Model *m) {
+  Exchange &x = m->x;
+  if (int rc = x_require_connected(m, "backward")) return rc;
+  const bool presorted = m->presorted && m->presort_sig == x_signature(m);
+  m->presorted = false;
+  FFEMB_CUDA_OK(cudaEventRecord(x.ev_grads, m->stream));  // this rank's gradient matrix is complete
+  if (x.n_rep) {
+    // replicas (the reference's data-parallel embedding): dense gradient of
+    // this rank's own samples -- the segment-reduce kernel with lr = -1 into a
+    // zeroed G; update() sums the replicas and applies the step
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(x.rep_stream, x.ev_grads, 0));
+    FFEMB_CUDA_OK(cudaMemsetAsync(x.buf + x.off_repG, 0, (size_t)x.rep_count * 4, x.rep_stream));
+    if (int rc = x_backward_groups(m, true, !presorted, true, -1.0f, x.rep_stream)) return rc;
+    x.rep_pending = true;
+  }
+  if (!presorted && x.n_owned)
+    if (int rc = x_backward_groups(m, false, true, false, 0.f, m->stream)) return rc;
+  // gradient exchange as a push: every sharded table's column block of this
+  // rank's gradient goes to its owner's staging matrix, rows [rank*Bs, ..)
+  {
+    std::vector<int> dims;
+    for (auto &op : m->ops)
+      if (!op->replicated && std::find(dims.begin(), dims.end(), op->D) == dims.end()) dims.push_back(op->D);
+    for (int D : dims) {
+      std::vector<ffemb_push_t> items;
+      for (auto &op : m->ops) {
+        if (op->replicated || op->D != D) continue;
+        const int q = op->owner;
+        ffemb_push_t it;
+        it.dst = (float *)(x.peer[q] + x.off_stage) + (int64_t)m->cfg.rank * x.Bs * x.stage_ld[q] + op->scol;
+        it.dst_ld = x.stage_ld[q];
+        it.src_col = op->gcol;
+        items.push_back(it);
+      }
+      if (int rc = ffemb_push_columns(items.data(), (int)items.size(), x.Bs, D,
+                                      (const float *)(x.buf + x.off_grad), x.ldx, m->stream))
+        return rc;
+    }
+  }
+  if (int rc = x_barrier(m, 0, m->stream)) return rc;  // the blocks have landed in the owners' staging
+  return FFEMB_OK;
+}
+
+static int x_update(Model *m) {
+  Exchange &x = m->x;
+  const float lr = (float)m->opt->lr;
+  if (x.n_owned)
+    if (int rc = x_backward_groups(m, false, false, true, lr, m->stream)) return rc;
+  if (x.rep_pending) {
+    float *W[kMaxParts];
+    const float *G[kMaxParts];
+    for (int q = 0; q < m->world; ++q) {
+      W[q] = (float *)(x.peer[q] + x.off_repW);
+      G[q] = (const float *)(x.peer[q] + x.off_repG);
+    }
+    if (int rc = x_barrier(m, 1, x.rep_stream)) return rc;  // every rank's replica gradient is complete
+    if (int rc = ffemb_replica_reduce_update(W, G, x.rep_count, m->cfg.rank, m->world, lr, x.rep_stream)) return rc;
+    if (int rc = x_barrier(m, 1, x.rep_stream)) return rc;  // every copy of the tables is written
+    FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_done, x.rep_stream));
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, x.ev_rep_done, 0));
+    x.rep_pending = false;
+  }
+  return FFEMB_OK;
+}
+
+// compile() for the sharded mode: placement, the exchange buffer, tables.
+static int x_compile(Model *m) {
+  Exchange &x = m->x;
+  const int B = m->cfg.batch_size, N = m->world, rank = m->cfg.rank;
+  if (N > kMaxParts) return fail(FFEMB_ERR_UNSUPPORTED, "compile: at most " + std::to_string(kMaxParts) + " ranks");
+  if (B % N) return fail(FFEMB_ERR_INVALID_ARGUMENT, "compile: the batch size must be divisible by the number of ranks");
+  x.on = true;
+  x.Bs = B / N;
+  int64_t below = m->cfg.replicate_below;
+  if (below < 0) below = x.Bs;  // a replica's all-reduce is cheaper than two exchanges iff N_t < B/N
+  if (N == 1 && !m->cfg.force_exchange) below = 0;
+  // placement: a strategy names the owners (FFMapper::slice_task); without one
+  // the sharded tables go round-robin, in table order, over the ranks
+  bool any_rep = false;
+  for (auto &op : m->ops) {
+    op->replicated = op->N < below;
+    any_rep = any_rep || op->replicated;
+  }
+  int k = 0;
+  for (auto &op : m->ops) {
+    if (op->replicated) {
+      op->owner = -1;
+      continue;
+    }
+    if (m->strategy.impl || !any_rep)
+      op->owner = ffemb_strategy_device_for_table(m->strategy, op->index, op->name.c_str(), N);
+    else
+      op->owner = k % N;
+    ++k;
+  }
+  // column layouts
+  x.stage_ld.assign(N, 0);
+  int64_t col = 0, rep_floats = 0;
+  std::vector<int64_t> rep_off(m->ops.size(), 0);
+  for (auto &op : m->ops) {
+    op->gcol = col;
+    col += op->D;
+    if (op->replicated) {
+      rep_off[op->index] = rep_floats;
+      rep_floats += (op->N * op->D + 3) / 4 * 4;
+      ++x.n_rep;
+    } else {
+      op->scol = x.stage_ld[op->owner];
+      x.stage_ld[op->owner] += op->D;
+      if (op->owner == rank) ++x.n_owned;
+    }
+  }
+  x.ldx = (col + 3) / 4 * 4;
+  for (int q = 0; q < N; ++q) x.stage_ld[q] = (std::max<int64_t>(x.stage_ld[q], 4) + 3) / 4 * 4;
+  x.rep_count = rep_floats;
+  // the one IPC-exportable allocation
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    const size_t o = off;
+    off += up256(bytes);
+    return o;
+  };
+  x.off_out = take((size_t)x.Bs * x.ldx * 4);
+  x.off_flags = take(256);
+  x.off_grad = take((size_t)x.Bs * x.ldx * 4);
+  x.off_repW = take((size_t)x.rep_count * 4);
+  x.off_repG = take((size_t)x.rep_count * 4);
+  x.off_stage = take(x.n_owned ? (size_t)B * x.stage_ld[rank] * 4 : 0);
+  x.bytes = off;
+  FFEMB_CUDA_OK(cudaMalloc((void **)&x.buf, x.bytes));
+  FFEMB_CUDA_OK(cudaMemsetAsync(x.buf, 0, x.bytes, m->stream));
+  x.peer[rank] = x.buf;
+  // tables (create_weights, embedding.cu:95-106); replicas live in the exchange
+  // buffer so that the owner of a slice can write every rank's copy
+  int64_t lookups = 0, entries = 0, rlookups = 0, rentries = 0;
+  int max_d = 1, rmax_d = 1;
+  for (auto &op : m->ops) {
+    const int L = op->input->dims[1];
+    if (op->replicated) {
+      op->W = (float *)(x.buf + x.off_repW) + rep_off[op->index];
+      op->G = (float *)(x.buf + x.off_repG) + rep_off[op->index];
+      rlookups += (int64_t)x.Bs * L;
+      rentries += op->N;
+      rmax_d = std::max(rmax_d, op->D);
+    } else if (op->owner == rank) {
+      FFEMB_CUDA_OK(cudaMalloc(&op->W, (size_t)op->N * op->D * sizeof(float)));
+      lookups += (int64_t)B * L;
+      entries += op->N;
+      max_d = std::max(max_d, op->D);
+    } else {
+      continue;
+    }
+    if (op->init.kind == Initializer::kZero) {
+      FFEMB_CUDA_OK(cudaMemsetAsync(op->W, 0, (size_t)op->N * op->D * sizeof(float), m->stream));
+    } else if (int rc = ffemb_uniform_init(op->W, op->N * op->D, op->init.seed, op->init.lo, op->init.hi,
+                                           m->stream)) {
+      return rc;
+    }
+  }
+  // every table's output / gradient block: a column block of this rank's matrices
+  for (auto &op : m->ops) {
+    op->output->data = Buffer{(float *)(x.buf + x.off_out) + op->gcol, x.ldx, false};
+    op->output->grad = Buffer{(float *)(x.buf + x.off_grad) + op->gcol, x.ldx, false};
+  }
+  if (x.n_owned) {
+    m->workspace_bytes = ffemb_embed_backward_workspace_bytes(lookups, entries, max_d) + ((size_t)(x.n_owned + 1) << 20);
+    FFEMB_CUDA_OK(cudaMalloc(&m->workspace, m->workspace_bytes));
+  }
+  if (x.n_rep) {
+    x.rep_ws_bytes = ffemb_embed_backward_workspace_bytes(rlookups, rentries, rmax_d) + ((size_t)(x.n_rep + 1) << 20);
+    FFEMB_CUDA_OK(cudaMalloc(&x.rep_ws, x.rep_ws_bytes));
+    FFEMB_CUDA_OK(cudaStreamCreateWithFlags(&x.rep_stream, cudaStreamNonBlocking));
+    FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_rep_fwd, cudaEventDisableTiming));
+    FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_rep_sorted, cudaEventDisableTiming));
+    FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_rep_done, cudaEventDisableTiming));
+  }
+  FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_grads, cudaEventDisableTiming));
+  x.connected = N == 1;
+  return FFEMB_OK;
+}
+
+static void x_destroy(Model *m) {
+  Exchange &x = m->x;
+  if (!x.on) return;
+  for (int q = 0; q < m->world; ++q)
+    if (q != m->cfg.rank && x.peer[q]) cudaIpcCloseMemHandle(x.peer[q]);
+  for (auto &op : m->ops)
+    if (op->replicated) op->W = nullptr;  // inside the exchange buffer
+  if (x.buf) cudaFree(x.buf);
+  if (x.rep_ws) cudaFree(x.rep_ws);
+  if (x.rep_stream) cudaStreamDestroy(x.rep_stream);
+  for (cudaEvent_t e : {x.ev_rep_fwd, x.ev_rep_sorted, x.ev_grads, x.ev_rep_done})
+    if (e) cudaEventDestroy(e);
+}
+
+}  // namespace ffemb
+
+using namespace ffemb;
+
+// ---- Sharded mode: connecting the ranks --------------------------------------
+extern "C" int ffemb_model_is_sharded(ffemb_model_t h) { return M(h) && M(h)->x.on ? 1 : 0; }
+
+extern "C" int ffemb_model_get_exchange_handle(ffemb_model_t h, uint8_t handle[64]) {
+  Model *m = M(h);
+  if (!m || !m->compiled || !m->x.on || !handle)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "get_exchange_handle: not a compiled sharded model");
+  FFEMB_CUDA_OK(cudaSetDevice(m->device));
+  FFEMB_CUDA_OK(cudaStreamSynchronize(m->stream));  // the buffer is zeroed before any peer can see it
+  return ffemb_ipc_get_handle(m->x.buf, handle);
+}
+
+extern "C" int ffemb_model_connect_peers(ffemb_model_t h, const uint8_t *handles, int count) {
+  Model *m = M(h);
+  if (!m || !m->compiled || !m->x.on || !handles)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "connect_peers: not a compiled sharded model");
+  if (count != m->world) return fail(FFEMB_ERR_INVALID_ARGUMENT, "connect_peers: one handle per rank is needed");
+  if (m->x.connected) return fail(FFEMB_ERR_INVALID_ARGUMENT, "connect_peers: already connected");
+  FFEMB_CUDA_OK(cudaSetDevice(m->device));
+  for (int q = 0; q < m->world; ++q) {
+    if (q == m->cfg.rank) continue;
+    void *p = nullptr;
+    if (int rc = ffemb_ipc_open_handle(handles + (size_t)q * 64, &p)) return rc;
+    m->x.peer[q] = (char *)p;
+  }
+  m->x.connected = true;
+  return FFEMB_OK;
+}
+
+extern "C" int ffemb_model_get_exchange_matrix(ffemb_model_t h, bool grad, float **ptr, int64_t *ld, int *rows) {
+  Model *m = M(h);
+  if (!m || !m->compiled || !m->x.on || !ptr || !ld || !rows)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "get_exchange_matrix: not a compiled sharded model");
+  *ptr = (float *)(m->x.buf + (grad ? m->x.off_grad : m->x.off_out));
+  *ld = m->x.ldx;
+  *rows = m->x.Bs;
+  return FFEMB_OK;
+}
+
 extern "C" int ffemb_model_compile(ffemb_model_t h) {
   Model *m = M(h);
   if (!m) return fail(FFEMB_ERR_INVALID_ARGUMENT, "compile: NULL model");
@@ -404,10 +890,15 @@ extern "C" int ffemb_model_compile(ffemb_model_t h) {
   } else {
     FFEMB_CUDA_OK(cudaGetDevice(&m->device));
   }
+  const bool sharded = m->world > 1 || m->cfg.force_exchange;
+  if (sharded) {
+    if (int rc = x_compile(m)) return rc;
+  }
   // placement: table i -> rank (FFMapper::slice_task, mapper.cc:33-97)
   int64_t lookups = 0, entries = 0, sum_d = 0;
   int max_d = 1, n_owned = 0;
   for (auto &op : m->ops) {
+    if (sharded) break;
     op->owner = ffemb_strategy_device_for_table(m->strategy, op->index, op->name.c_str(), m->world);
     if (!owned(op.get())) continue;
     ++n_owned;
@@ -419,7 +910,7 @@ extern "C" int ffemb_model_compile(ffemb_model_t h) {
   const int B = m->cfg.batch_size;
   // tables + initialisers (create_weights, embedding.cu:95-106; model.cc:692-696)
   for (auto &op : m->ops) {
-    if (!owned(op.get())) continue;
+    if (sharded || !owned(op.get())) continue;
     FFEMB_CUDA_OK(cudaMalloc(&op->W, (size_t)op->N * op->D * sizeof(float)));
     if (op->init.kind == Initializer::kZero) {
       FFEMB_CUDA_OK(cudaMemsetAsync(op->W, 0, (size_t)op->N * op->D * sizeof(float), m->stream));
@@ -431,7 +922,7 @@ extern "C" int ffemb_model_compile(ffemb_model_t h) {
   // outputs and their gradients: one [B][sum D] matrix each, so the owned
   // tables' blocks already sit side by side as Concat would lay them out
   // (src/ops/concat.cu:159-215).
-  if (n_owned) {
+  if (n_owned && !sharded) {
     m->mat_ld = (sum_d + 3) / 4 * 4;
     FFEMB_CUDA_OK(cudaMalloc(&m->out_mat, (size_t)B * m->mat_ld * sizeof(float)));
     FFEMB_CUDA_OK(cudaMalloc(&m->grad_mat, (size_t)B * m->mat_ld * sizeof(float)));
@@ -520,6 +1011,7 @@ static std::vector<int64_t> sort_signature(Model *m) {
 extern "C" int ffemb_model_forward(ffemb_model_t h) {
   Model *m = M(h);
   if (int rc = ready(m, "forward")) return rc;
+  if (m->x.on) return x_forward(m);
   // Training: fork the key sort of the coming backward onto the side stream.
   // It reads only the index tensors, which are complete at this point of the
   // model stream, and it is small and latency-bound, so it hides under the
@@ -556,6 +1048,10 @@ extern "C" int ffemb_model_forward(ffemb_model_t h) {
 extern "C" int ffemb_model_zero_gradients(ffemb_model_t h) {
   Model *m = M(h);
   if (int rc = ready(m, "zero_gradients")) return rc;
+  if (m->x.on && m->sorted)
+    return fail(FFEMB_ERR_UNSUPPORTED,
+                "zero_gradients: in sharded mode a backward() must be followed by update() on every "
+                "rank (the ranks' barriers are counted)");
   m->sorted = false;  // the (sparse) table gradient is now empty
   return FFEMB_OK;
 }
@@ -563,6 +1059,19 @@ extern "C" int ffemb_model_zero_gradients(ffemb_model_t h) {
 extern "C" int ffemb_model_backward(ffemb_model_t h) {
   Model *m = M(h);
   if (int rc = ready(m, "backward")) return rc;
+  // The reference's backward ACCUMULATES into the table gradient
+  // (embedding.cu:350-352, READ_WRITE region); the sparse gradient kept here
+  // describes one batch only, so a second backward() before update() /
+  // zero_gradients() is refused instead of silently replacing the first.
+  if (m->sorted)
+    return fail(FFEMB_ERR_UNSUPPORTED,
+                "backward: a gradient is already pending; gradient accumulation over several "
+                "backward() calls is not supported -- call update() or zero_gradients() first");
+  if (m->x.on) {
+    if (int rc = x_backward(m)) return rc;
+    m->sorted = true;
+    return FFEMB_OK;
+  }
   if (m->presorted && m->presort_sig == sort_signature(m)) {
     m->presorted = false;  // forward() already sorted these indices
   } else {
@@ -581,6 +1090,11 @@ extern "C" int ffemb_model_update(ffemb_model_t h) {
                 "update: the sparse fused SGD equals the reference's dense sgd_update only for "
                 "momentum == 0 and weight_decay == 0");
   if (!m->sorted) return FFEMB_OK;  // zero gradient: W -= lr*0
+  if (m->x.on) {
+    if (int rc = x_update(m)) return rc;
+    m->sorted = false;
+    return FFEMB_OK;
+  }
   if (int rc = backward_phase(m, false, true, m->stream)) return rc;
   m->sorted = false;
   return FFEMB_OK;
@@ -619,6 +1133,205 @@ extern "C" ffemb_tensor_t ffemb_op_get_output_by_id(ffemb_op_t h, int id) {
 extern "C" const char *ffemb_op_get_name(ffemb_op_t h) { return O(h) ? O(h)->name.c_str() : nullptr; }
 extern "C" int ffemb_op_get_device(ffemb_op_t h) { return O(h) ? O(h)->owner : -1; }
 
+// ===========================================================================
+// Host ingest / egress, double-buffered.
+//
+// The reference stages every table's indices per step through a freshly
+// allocated pinned buffer and a synchronous cudaMemcpy (examples/cpp/DLRM/
+// dlrm.cu:19-56, called from DataLoader::next_batch, dlrm.cc:486-524), and
+// keeps embedding outputs and their gradients in zero-copy host memory
+// (src/ops/embedding.cu:280-284,343-347).  Here the host side of a step is
+// three asynchronous library calls over two slots of device buffers and two
+// copy streams, so the H2D of batch i+1 and the D2H of batch i-1 run under
+// the kernels of batch i (PCIe is full duplex):
+//   load_batch_async      indices (+ upstream gradients) of the NEXT batch,
+//                         host -> the idle slot, on the copy-in stream
+//   begin_batch           the loaded slot becomes current (stream-ordered)
+//   fetch_outputs_async   pooled outputs of the current batch -> host, on the
+//                         copy-out stream, after forward()
+// ===========================================================================
+namespace ffemb {
+
+struct HostPipe {
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_fwd[2] = {}, ev_out[2] = {};
+  bool done_rec[2] = {false, false}, out_rec[2] = {false, false}, loaded[2] = {false, false};
+  std::vector<int64_t *> idx[2];  // per op: device index buffer of the slot (nullptr: not read by this rank)
+  float *out[2] = {}, *grad[2] = {};  // [rows][ld] per slot (sharded: staging next to the exchange matrices)
+  int64_t ld = 0;
+  int rows = 0;
+  int64_t width = 0;  // sum of out_dim over all tables = row length of the host matrices
+  int next = 0, cur = -1;
+  int last_fetch = -1, prev_fetch = -1;
+};
+
+static void pipe_destroy(Model *m) {
+  HostPipe *p = m->pipe;
+  if (!p) return;
+  for (int s = 0; s < 2; ++s) {
+    for (int64_t *b : p->idx[s])
+      if (b) cudaFree(b);
+    // slot 0 of an unsharded model borrows the model's own matrices
+    if (p->out[s] && p->out[s] != m->out_mat) cudaFree(p->out[s]);
+    if (p->grad[s] && p->grad[s] != m->grad_mat) cudaFree(p->grad[s]);
+    for (cudaEvent_t e : {p->ev_in[s], p->ev_done[s], p->ev_fwd[s], p->ev_out[s]})
+      if (e) cudaEventDestroy(e);
+  }
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
+  delete p;
+  m->pipe = nullptr;
+}
+
+static bool reads_indices(const Model *m, const Op *op) { return op->replicated || owned(op); }
+
+static int pipe_create(Model *m) {
+  if (m->pipe) return FFEMB_OK;
+  auto p = std::make_unique<HostPipe>();
+  const int B = m->cfg.batch_size;
+  FFEMB_CUDA_OK(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
+  FFEMB_CUDA_OK(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
+  for (auto &op : m->ops) p->width += op->D;
+  if (m->x.on) {
+    p->rows = m->x.Bs;
+    p->ld = m->x.ldx;
+  } else {
+    p->rows = B;
+    p->ld = (p->width + 3) / 4 * 4;
+    for (auto &op : m->ops)
+      if (!owned(op.get()))
+        return fail(FFEMB_ERR_UNSUPPORTED, "host pipeline: every table must be held by this rank");
+  }
+  m->pipe = p.release();  // from here on pipe_destroy cleans up after a failure
+  HostPipe *q = m->pipe;
+  for (int s = 0; s < 2; ++s) {
+    for (cudaEvent_t *e : {&q->ev_in[s], &q->ev_done[s], &q->ev_fwd[s], &q->ev_out[s]})
+      FFEMB_CUDA_OK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    q->idx[s].assign(m->ops.size(), nullptr);
+    for (auto &op : m->ops)
+      if (reads_indices(m, op.get()))
+        FFEMB_CUDA_OK(cudaMalloc(&q->idx[s][op->index], (size_t)B * op->input->dims[1] * sizeof(int64_t)));
+    const size_t bytes = (size_t)q->rows * q->ld * sizeof(float);
+    if (!m->x.on && s == 0 && m->out_mat && m->mat_ld == q->ld) {
+      q->out[0] = m->out_mat;
+      q->grad[0] = m->grad_mat;
+    } else {
+      FFEMB_CUDA_OK(cudaMalloc(&q->out[s], bytes));
+      FFEMB_CUDA_OK(cudaMalloc(&q->grad[s], bytes));
+      FFEMB_CUDA_OK(cudaMemsetAsync(q->grad[s], 0, bytes, m->stream));
+    }
+  }
+  return FFEMB_OK;
+}
+
+}  // namespace ffemb
+
+using namespace ffemb;
+
+extern "C" int ffemb_model_load_batch_async(ffemb_model_t h, const int64_t *const *indices, const float *out_grad) {
+  Model *m = M(h);
+  if (!m || !m->compiled) return fail(FFEMB_ERR_INVALID_ARGUMENT, "load_batch_async: model is not compiled");
+  if (!indices) return fail(FFEMB_ERR_INVALID_ARGUMENT, "load_batch_async: indices is NULL");
+  FFEMB_CUDA_OK(cudaSetDevice(m->device));
+  if (int rc = pipe_create(m)) return rc;
+  HostPipe *p = m->pipe;
+  const int s = p->next;
+  if (p->loaded[s]) return fail(FFEMB_ERR_INVALID_ARGUMENT, "load_batch_async: both slots hold a batch; call begin_batch");
+  // the slot's previous batch has been consumed (kernels) and its outputs fetched
+  if (p->done_rec[s]) FFEMB_CUDA_OK(cudaStreamWaitEvent(p->s_in, p->ev_done[s], 0));
+  const int B = m->cfg.batch_size;
+  for (auto &op : m->ops) {
+    int64_t *dst = p->idx[s][op->index];
+    if (!dst) continue;
+    const int64_t *src = indices[op->index];
+    if (!src)
+      return fail(FFEMB_ERR_INVALID_ARGUMENT, "load_batch_async: no indices for " + op->name + ", which this rank reads");
+    const int L = op->input->dims[1];
+    int64_t first = 0, cnt = (int64_t)B * L;
+    if (op->replicated) {  // only this rank's own samples of a replicated table are read
+      cnt = (int64_t)m->x.Bs * L;
+      first = (int64_t)m->cfg.rank * cnt;
+    }
+    FFEMB_CUDA_OK(cudaMemcpyAsync(dst + first, src + first, cnt * sizeof(int64_t), cudaMemcpyHostToDevice, p->s_in));
+  }
+  if (out_grad)
+    FFEMB_CUDA_OK(cudaMemcpy2DAsync(p->grad[s], p->ld * sizeof(float), out_grad, p->width * sizeof(float),
+                                    p->width * sizeof(float), p->rows, cudaMemcpyHostToDevice, p->s_in));
+  FFEMB_CUDA_OK(cudaEventRecord(p->ev_in[s], p->s_in));
+  p->loaded[s] = true;
+  p->next = s ^ 1;
+  return FFEMB_OK;
+}
+
+extern "C" int ffemb_model_begin_batch(ffemb_model_t h) {
+  Model *m = M(h);
+  if (!m || !m->compiled || !m->pipe) return fail(FFEMB_ERR_INVALID_ARGUMENT, "begin_batch: no batch was loaded");
+  FFEMB_CUDA_OK(cudaSetDevice(m->device));
+  HostPipe *p = m->pipe;
+  const int s = p->cur < 0 ? 0 : p->cur ^ 1;
+  if (!p->loaded[s]) return fail(FFEMB_ERR_INVALID_ARGUMENT, "begin_batch: the next slot holds no batch; call load_batch_async");
+  if (p->cur >= 0) {  // everything that used the old slot has been enqueued by now
+    FFEMB_CUDA_OK(cudaEventRecord(p->ev_done[p->cur], m->stream));
+    p->done_rec[p->cur] = true;
+  }
+  FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, p->ev_in[s], 0));
+  if (p->out_rec[s]) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, p->ev_out[s], 0));  // its outputs have left
+  for (auto &op : m->ops) {
+    if (p->idx[s][op->index]) {
+      release(op->input->data);
+      op->input->data = Buffer{p->idx[s][op->index], op->input->dims[1], false};
+    }
+    if (!m->x.on) {  // the slot's matrices ARE the outputs / gradients of this batch
+      int64_t col = 0;
+      for (auto &o2 : m->ops) {
+        if (o2.get() == op.get()) break;
+        col += o2->D;
+      }
+      release(op->output->data);
+      release(op->output->grad);
+      op->output->data = Buffer{p->out[s] + col, p->ld, false};
+      op->output->grad = Buffer{p->grad[s] + col, p->ld, false};
+    }
+  }
+  if (m->x.on)  // the exchange matrices are fixed (peers hold their addresses): copy in
+    FFEMB_CUDA_OK(cudaMemcpyAsync(m->x.buf + m->x.off_grad, p->grad[s], (size_t)p->rows * p->ld * sizeof(float),
+                                  cudaMemcpyDeviceToDevice, m->stream));
+  m->presorted = false;
+  p->loaded[s] = false;
+  p->cur = s;
+  return FFEMB_OK;
+}
+
+extern "C" int ffemb_model_fetch_outputs_async(ffemb_model_t h, float *out_host) {
+  Model *m = M(h);
+  if (!m || !m->compiled || !m->pipe || m->pipe->cur < 0 || !out_host)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "fetch_outputs_async: no current batch (begin_batch) or NULL buffer");
+  FFEMB_CUDA_OK(cudaSetDevice(m->device));
+  HostPipe *p = m->pipe;
+  const int s = p->cur;
+  if (m->x.on)
+    FFEMB_CUDA_OK(cudaMemcpyAsync(p->out[s], m->x.buf + m->x.off_out, (size_t)p->rows * p->ld * sizeof(float),
+                                  cudaMemcpyDeviceToDevice, m->stream));
+  FFEMB_CUDA_OK(cudaEventRecord(p->ev_fwd[s], m->stream));
+  FFEMB_CUDA_OK(cudaStreamWaitEvent(p->s_out, p->ev_fwd[s], 0));
+  FFEMB_CUDA_OK(cudaMemcpy2DAsync(out_host, p->width * sizeof(float), p->out[s], p->ld * sizeof(float),
+                                  p->width * sizeof(float), p->rows, cudaMemcpyDeviceToHost, p->s_out));
+  FFEMB_CUDA_OK(cudaEventRecord(p->ev_out[s], p->s_out));
+  p->out_rec[s] = true;
+  p->prev_fetch = p->last_fetch;
+  p->last_fetch = s;
+  return FFEMB_OK;
+}
+
+extern "C" int ffemb_model_wait_outputs(ffemb_model_t h, bool all) {
+  Model *m = M(h);
+  if (!m || !m->pipe) return FFEMB_OK;
+  HostPipe *p = m->pipe;
+  if (p->prev_fetch >= 0 && p->prev_fetch != p->last_fetch) FFEMB_CUDA_OK(cudaEventSynchronize(p->ev_out[p->prev_fetch]));
+  if (all && p->last_fetch >= 0) FFEMB_CUDA_OK(cudaEventSynchronize(p->ev_out[p->last_fetch]));
+  return FFEMB_OK;
+}
+
 // ---- Tensor data -------------------------------------------------------------
 static Op *consumer_of(Tensor *t) {
   for (auto &op : t->model->ops)
@@ -640,16 +1353,24 @@ extern "C" int ffemb_tensor_set_int64(ffemb_tensor_t h, ffemb_model_t model, con
     return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_set_int64: count != batch * bag_size");
   // indices are only needed where the consuming table lives (the reference's
   // loader also loads table t's indices on table t's device, dlrm.cc:491-524)
-  bool needed = false;
-  for (auto &op : m->ops) needed = needed || (op->input == t && owned(op.get()));
-  if (!needed) return FFEMB_OK;
+  bool needed = false, slice = false;
+  for (auto &op : m->ops) {
+    needed = needed || (op->input == t && owned(op.get()));
+    slice = slice || (op->input == t && op->replicated);  // a replica reads this rank's own samples only
+  }
+  if (!needed && !slice) return FFEMB_OK;
   if (!t->data.ptr) {
     void *p = nullptr;
     FFEMB_CUDA_OK(cudaMalloc(&p, n * sizeof(int64_t)));
     t->data = Buffer{p, t->dims[1], true};
   }
-  FFEMB_CUDA_OK(cudaMemcpyAsync(t->data.ptr, data, n * sizeof(int64_t), cudaMemcpyHostToDevice,
-                                m->stream));
+  int64_t first = 0, cnt = n;
+  if (!needed) {
+    cnt = (int64_t)m->x.Bs * t->dims[1];
+    first = (int64_t)m->cfg.rank * cnt;
+  }
+  FFEMB_CUDA_OK(cudaMemcpyAsync((int64_t *)t->data.ptr + first, data + first, cnt * sizeof(int64_t),
+                                cudaMemcpyHostToDevice, m->stream));
   m->presorted = false;  // keys sorted during forward() belong to the old contents
   return FFEMB_OK;
 }
@@ -662,11 +1383,15 @@ extern "C" int ffemb_tensor_set_grad_float(ffemb_tensor_t h, ffemb_model_t model
     return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_set_grad_float: bad arguments");
   if (int rc = ready(m, "tensor_set_grad_float")) return rc;
   if (!t->producer) return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_set_grad_float: not an embedding output");
-  if (count != (int64_t)t->dims[0] * t->dims[1])
-    return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_set_grad_float: count != batch * out_dim");
-  if (!owned(t->producer)) return FFEMB_OK;
+  // sharded mode: every rank holds the gradient of ITS samples for every table
+  const int rows = m->x.on ? m->x.Bs : t->dims[0];
+  if (count != (int64_t)rows * t->dims[1])
+    return fail(FFEMB_ERR_INVALID_ARGUMENT,
+                m->x.on ? "tensor_set_grad_float: count != (batch / ranks) * out_dim"
+                        : "tensor_set_grad_float: count != batch * out_dim");
+  if (!m->x.on && !owned(t->producer)) return FFEMB_OK;
   FFEMB_CUDA_OK(cudaMemcpy2DAsync(t->grad.ptr, t->grad.ld * sizeof(float), data,
-                                  t->dims[1] * sizeof(float), t->dims[1] * sizeof(float), t->dims[0],
+                                  t->dims[1] * sizeof(float), t->dims[1] * sizeof(float), rows,
                                   cudaMemcpyHostToDevice, m->stream));
   return FFEMB_OK;
 }
@@ -678,12 +1403,15 @@ extern "C" int ffemb_tensor_get_float(ffemb_tensor_t h, ffemb_model_t model, flo
   if (!t || !m || t->model != m || !data)
     return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_get_float: bad arguments");
   if (int rc = ready(m, "tensor_get_float")) return rc;
-  if (!t->producer || !owned(t->producer))
+  if (!t->producer || (!m->x.on && !owned(t->producer)))
     return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_get_float: not an output of a table this rank owns");
-  if (count != (int64_t)t->dims[0] * t->dims[1])
-    return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_get_float: count != batch * out_dim");
+  // sharded mode: this rank's samples of every table's output
+  const int rows = m->x.on ? m->x.Bs : t->dims[0];
+  if (count != (int64_t)rows * t->dims[1])
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, m->x.on ? "tensor_get_float: count != (batch / ranks) * out_dim"
+                                                    : "tensor_get_float: count != batch * out_dim");
   FFEMB_CUDA_OK(cudaMemcpy2DAsync(data, t->dims[1] * sizeof(float), t->data.ptr,
-                                  t->data.ld * sizeof(float), t->dims[1] * sizeof(float), t->dims[0],
+                                  t->data.ld * sizeof(float), t->dims[1] * sizeof(float), rows,
                                   cudaMemcpyDeviceToHost, m->stream));
   FFEMB_CUDA_OK(cudaStreamSynchronize(m->stream));
   return FFEMB_OK;
@@ -699,6 +1427,10 @@ extern "C" int ffemb_tensor_attach_device_ptr(ffemb_tensor_t h, void *device_ptr
     return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_attach_device_ptr: index tensors have no gradient");
   if (!t->producer && ld != t->dims[t->num_dims - 1])
     return fail(FFEMB_ERR_INVALID_ARGUMENT, "tensor_attach_device_ptr: index tensors must be contiguous (ld == bag size)");
+  if (t->producer && t->model->x.on)
+    return fail(FFEMB_ERR_UNSUPPORTED,
+                "tensor_attach_device_ptr: in sharded mode outputs and gradients live in the library's "
+                "peer-mapped exchange buffer (ffemb_model_get_exchange_matrix)");
   Buffer &b = grad ? t->grad : t->data;
   if (b.owned && b.ptr) {
     if (t->model->compiled) cudaSetDevice(t->model->device);
@@ -726,7 +1458,7 @@ extern "C" bool ffemb_parameter_set_weights_float(ffemb_parameter_t h, ffemb_mod
   }
   if (ready(m, "parameter_set_weights_float")) return false;
   Op *op = p->op;
-  if (!owned(op)) {
+  if (!owned(op) && !op->replicated) {
     set_error("parameter_set_weights_float: table " + op->name + " is owned by rank " +
               std::to_string(op->owner));
     return false;
@@ -756,7 +1488,7 @@ extern "C" bool ffemb_parameter_get_weights_float(ffemb_parameter_t h, ffemb_mod
   }
   if (ready(m, "parameter_get_weights_float")) return false;
   Op *op = p->op;
-  if (!owned(op)) {
+  if (!owned(op) && !op->replicated) {
     set_error("parameter_get_weights_float: table " + op->name + " is owned by rank " +
               std::to_string(op->owner));
     return false;

@@ -260,6 +260,18 @@ typedef struct ffemb_push_t {
 int ffemb_push_columns(const ffemb_push_t *items, int num_items, int rows,
                        int width, const float *src, int64_t src_ld,
                        void *stream);
+/* Replicated small tables: sum of the ranks' dense gradient replicas fused
+ * with the SGD step, over peer memory.  weights[q] / grads[q] (HOST arrays of
+ * device pointers, 16-byte aligned) are the mapped bases of rank q's flat
+ * [count] copy of the replicated tables and of its dense gradient.  Rank r
+ * handles the r-th slice: loads that slice of every rank's gradient, adds
+ * them in rank order (replica 0 += replica q, src/runtime/
+ * optimizer_kernel.cu:96-101), applies W = fmaf(-lr, sum, W) (sgd_update,
+ * :23-41) and stores the result into every rank's copy.  Bracket it with two
+ * ffemb_peer_barrier calls: gradients complete before, copies written after. */
+int ffemb_replica_reduce_update(float *const *weights, const float *const *grads,
+                                int64_t count, int rank, int world, float lr,
+                                void *stream);
 
 /* ------------------------------------------------------------------------
  * (M) Model-level entry points (flexflow_c.h surface for this path)
@@ -296,6 +308,18 @@ int ffemb_config_set_rank(ffemb_config_t handle, int rank, int cuda_device);
 int ffemb_config_get_rank(ffemb_config_t handle);
 /* "--import[-strategy] <file>" (src/mapper/mapper.cc:282-286). */
 int ffemb_config_import_strategy_file(ffemb_config_t handle, const char *path);
+/* With more than one rank: tables with fewer than `rows` rows are kept on
+ * EVERY rank instead of sharded -- the reference's data-parallel embedding
+ * (replicated table, gradient replicas summed: src/runtime/model.cc:697-724,
+ * optimizer_kernel.cu:96-101) -- because for them one sum of the dense
+ * gradient replicas is cheaper than two exchanges of pooled rows.  0 (the
+ * default): shard everything, as the reference's strategy files do; -1: the
+ * break-even batch / ranks.  Without a strategy the remaining sharded tables
+ * are dealt round-robin, in table order, over the ranks. */
+int ffemb_config_set_replicate_below(ffemb_config_t handle, int64_t rows);
+/* Run the sharded engine (exchange buffer, barriers, staging) even with one
+ * rank.  For tests on a single GPU. */
+int ffemb_config_set_exchange_engine(ffemb_config_t handle, int force);
 
 /* --- FFModel (flexflow_c.h:86-135) */
 ffemb_model_t ffemb_model_create(ffemb_config_t config);
@@ -333,12 +357,50 @@ int ffemb_model_set_sgd_optimizer(ffemb_model_t handle,
  * workspace.  Loss/metrics arguments of the reference do not exist on this
  * path. */
 int ffemb_model_compile(ffemb_model_t handle);
+/* --- Sharded mode (workers_per_node * num_nodes > 1; one process per GPU).
+ * The same program runs on every rank: all tables are added on all ranks,
+ * compile() places them (strategy -> owner, FFMapper::slice_task) and
+ * allocates, per rank, the tables it owns plus ONE exchange buffer holding
+ * its [batch/ranks][sum out_dim] output and gradient matrices (every table's
+ * block side by side: the reference's Concat layout), the barrier words, the
+ * replicated tables and the gradient staging.  The ranks then swap the 64-byte
+ * IPC handles of those buffers out of band (torch.distributed, MPI, a file):
+ * every rank calls get_exchange_handle, gathers all ranks' handles in rank
+ * order and passes them to connect_peers.  After that
+ *   forward()   gathers the whole batch for the tables this rank owns and
+ *               stores each pooled row straight into the consuming rank's
+ *               matrix over NVLink; replicated tables are gathered locally;
+ *               a peer-memory barrier ends it;
+ *   backward()  pushes every sharded table's block of this rank's gradient
+ *               matrix into its owner's staging and builds the replicas' dense
+ *               gradients; barrier;
+ *   update()    applies the sparse SGD step to the owned tables and, for the
+ *               replicas, sums the ranks' gradients and writes the stepped
+ *               rows into every rank's copy in one kernel over peer memory.
+ * Stands in for the reference's implicit repartition at Concat
+ * (src/ops/concat.cu:85-93; embedding.cu:280-284,343-347) and the mapper's
+ * placement (src/mapper/mapper.cc:33-97).  Output tensors then describe this
+ * rank's samples: get_float / set_grad_float take (batch/ranks)*out_dim
+ * values, get_device_ptr points into the exchange matrices.  Work that
+ * consumes the outputs or produces the gradients must be enqueued on the
+ * model's stream; every rank must make the same calls in the same order. */
+int ffemb_model_is_sharded(ffemb_model_t handle);
+int ffemb_model_get_exchange_handle(ffemb_model_t handle, uint8_t ipc_handle[64]);
+/* `handles`: count * 64 bytes, rank q's handle at handles + 64*q. */
+int ffemb_model_connect_peers(ffemb_model_t handle, const uint8_t *handles, int count);
+/* This rank's [batch/ranks][ld] output (grad = false) or gradient matrix. */
+int ffemb_model_get_exchange_matrix(ffemb_model_t handle, bool grad, float **ptr,
+                                    int64_t *ld, int *rows);
+
 /* flexflow_model_init_layers (:98-100) -- EMBED_INIT_TASK is a no-op in the
  * reference too (src/ops/embedding.cu:137-144). */
 int ffemb_model_init_layers(ffemb_model_t handle);
 /* flexflow_model_forward / zero_gradients / backward / update (:106-135).
  * zero_gradients is a no-op: no dense gradient exists.  backward builds the
- * sorted sparse gradient; update applies SGD to the touched rows. */
+ * sorted sparse gradient; update applies SGD to the touched rows.  The
+ * reference's backward accumulates into the dense gradient (embedding.cu:
+ * 350-352); here a second backward() before update() / zero_gradients()
+ * returns FFEMB_ERR_UNSUPPORTED instead of replacing the first gradient. */
 int ffemb_model_forward(ffemb_model_t handle);
 int ffemb_model_zero_gradients(ffemb_model_t handle);
 int ffemb_model_backward(ffemb_model_t handle);
@@ -374,6 +436,37 @@ int ffemb_tensor_set_grad_float(ffemb_tensor_t handle, ffemb_model_t model,
 /* Device -> host copy of a float tensor (an embedding output). */
 int ffemb_tensor_get_float(ffemb_tensor_t handle, ffemb_model_t model,
                            float *data, int64_t count);
+/* --- Double-buffered host ingest / egress.  The reference stages every
+ * table's indices per step through a freshly allocated pinned buffer and a
+ * synchronous cudaMemcpy (examples/cpp/DLRM/dlrm.cu:19-56, from
+ * DataLoader::next_batch, dlrm.cc:486-524) and keeps embedding outputs and
+ * their gradients in zero-copy host memory (src/ops/embedding.cu:280-284,
+ * 343-347).  Here two slots of device buffers and two library-owned copy
+ * streams let the H2D of batch i+1 and the D2H of batch i-1 run under the
+ * kernels of batch i.  Per step:
+ *     ffemb_model_begin_batch(m);             the loaded slot becomes current
+ *     ffemb_model_forward(m);
+ *     ffemb_model_fetch_outputs_async(m, o);  pooled outputs -> host
+ *     ffemb_model_zero_gradients(m); ffemb_model_backward(m); ffemb_model_update(m);
+ *     ffemb_model_load_batch_async(m, idx, g);   the NEXT batch, host -> idle slot
+ *     ffemb_model_wait_outputs(m, false);     the previous step's outputs are on the host
+ * (one ffemb_model_load_batch_async before the first step).  Host buffers
+ * should be pinned.  `indices[i]`: host [batch][bag] int64 of layer i (NULL for
+ * a table this rank does not read; of a replicated table only this rank's own
+ * samples are copied).  `out_grad` (may be NULL) and `out_host`: host
+ * [rows][sum of out_dim] fp32, every table's block side by side in layer
+ * order, rows = batch (one rank) or batch / ranks (sharded: this rank's
+ * samples).  While the pipeline is in use it owns the tensors' buffers:
+ * output / gradient blocks attached with ffemb_tensor_attach_device_ptr are
+ * replaced. */
+int ffemb_model_load_batch_async(ffemb_model_t handle, const int64_t *const *indices,
+                                 const float *out_grad);
+int ffemb_model_begin_batch(ffemb_model_t handle);
+int ffemb_model_fetch_outputs_async(ffemb_model_t handle, float *out_host);
+/* Blocks the host until every fetch but the most recent one has landed (all
+ * of them when `all` is true). */
+int ffemb_model_wait_outputs(ffemb_model_t handle, bool all);
+
 /* Borrow caller-owned device memory instead of the library's own buffer
  * (torch tensors: data_ptr()).  `ld` is the row stride in elements; for an
  * output tensor, attaching column blocks of one [batch][T*D] matrix yields
