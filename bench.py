@@ -304,6 +304,7 @@ def run_ours(args, w):
     cfg.set_rank(rank, local_rank)
     if world > 1:
         cfg.set_replicate_below({"auto": -1, "off": 0}.get(args.replicate, args.replicate))
+        cfg.set_gradient_exchange(os.environ.get("FFEMB_BWD", "auto"))
     m = ff.FFModel(cfg)
     m.set_stream(stream.cuda_stream)
     if world > 1 and args.placement == "balance":
@@ -424,11 +425,17 @@ def run_ours(args, w):
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
+    tracing = world > 1 and os.environ.get("FFEMB_TRACE") == "1" and not args.graph
+    if tracing:
+        m.trace(True)
     for i in range(K):
         step((args.warmup + i) % args.pool, evs[i])
         if flush is not None:
             flush.zero_()
     torch.cuda.synchronize()
+    if tracing:
+        m.trace(False)
+        sys.stderr.write("TRACE " + m.trace_report() + "\n")
     if dist is not None:
         dist.barrier()
     launches = kernels.kernel_launch_count() - launches0

@@ -98,6 +98,7 @@ SIGNATURES = {
     "ffemb_config_import_strategy_file": (_i, [_H, _cp]),
     "ffemb_config_set_replicate_below": (_i, [_H, _i64]),
     "ffemb_config_set_exchange_engine": (_i, [_H, _i]),
+    "ffemb_config_set_gradient_exchange": (_i, [_H, _i]),
     # model
     "ffemb_model_create": (_H, [_H]),
     "ffemb_model_destroy": (None, [_H]),
@@ -120,6 +121,8 @@ SIGNATURES = {
     "ffemb_model_get_layer_by_id": (_H, [_H, _i]),
     "ffemb_model_set_strategy": (_i, [_H, _H]),
     "ffemb_model_is_sharded": (_i, [_H]),
+    "ffemb_model_trace": (_i, [_H, _i]),
+    "ffemb_model_trace_report": (_sz, [_H, _vp, _sz]),
     "ffemb_model_get_exchange_handle": (_i, [_H, _vp]),
     "ffemb_model_connect_peers": (_i, [_H, _vp, _i]),
     "ffemb_model_get_exchange_matrix": (_i, [_H, _b, C.POINTER(C.c_void_p), C.POINTER(_i64), _ip]),

@@ -136,6 +136,10 @@ class FFConfig(_Owned):
         batch / ranks, where a replica becomes cheaper than a shard."""
         check(lib().ffemb_config_set_replicate_below(self.handle, -1 if rows == "auto" else int(rows)))
 
+    def set_gradient_exchange(self, mode):
+        """'auto' (pull with two ranks, push from three up), 'push' or 'pull'."""
+        check(lib().ffemb_config_set_gradient_exchange(self.handle, {"auto": 0, "push": 1, "pull": 2}[mode]))
+
     def set_exchange_engine(self, force=True):
         """Run the sharded engine even with one rank (single-GPU tests)."""
         check(lib().ffemb_config_set_exchange_engine(self.handle, int(bool(force))))
@@ -505,6 +509,15 @@ class FFModel(_Owned):
 
     def wait_outputs(self, all=False):
         check(lib().ffemb_model_wait_outputs(self.handle, bool(all)))
+
+    def trace(self, enable=True):
+        check(lib().ffemb_model_trace(self.handle, int(enable)))
+
+    def trace_report(self):
+        n = lib().ffemb_model_trace_report(self.handle, None, 0)
+        buf = C.create_string_buffer(n + 16)
+        lib().ffemb_model_trace_report(self.handle, buf, n + 16)
+        return buf.value.decode()
 
     def is_sharded(self):
         return bool(lib().ffemb_model_is_sharded(self.handle))

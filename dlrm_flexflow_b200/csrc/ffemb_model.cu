@@ -27,6 +27,7 @@ struct Config {
   std::string strategy_file;
   int64_t replicate_below = 0;  // world > 1: tables with fewer rows live on every rank; -1 = batch / world
   int force_exchange = 0;       // run the sharded engine even with one rank (tests)
+  int grad_exchange = 0;        // 0 auto (pull for 2 ranks, push from 3 up), 1 push, 2 pull
 };
 
 struct Initializer {
@@ -104,6 +105,11 @@ struct Exchange {
   cudaStream_t rep_stream = nullptr;
   cudaEvent_t ev_rep_fwd = nullptr, ev_rep_sorted = nullptr, ev_grads = nullptr, ev_rep_done = nullptr;
   bool rep_pending = false;   // backward() left a replica gradient for update() to reduce
+  bool pull = false;          // gradient exchange: the update kernel loads rows from the peers' matrices
+  cudaStream_t rep_side = nullptr;  // high priority: the replicas' key sort
+  // development aid: timed events at the phase boundaries of a step (all streams)
+  bool trace = false;
+  std::vector<std::pair<const char *, cudaEvent_t>> marks;
 };
 
 struct Model {
@@ -250,6 +256,11 @@ extern "C" int ffemb_config_get_rank(ffemb_config_t h) { return C(h) ? C(h)->ran
 extern "C" int ffemb_config_set_replicate_below(ffemb_config_t h, int64_t rows) {
   if (!C(h) || rows < -1) return fail(FFEMB_ERR_INVALID_ARGUMENT, "config_set_replicate_below: bad argument");
   C(h)->replicate_below = rows;
+  return FFEMB_OK;
+}
+extern "C" int ffemb_config_set_gradient_exchange(ffemb_config_t h, int mode) {
+  if (!C(h) || mode < 0 || mode > 2) return fail(FFEMB_ERR_INVALID_ARGUMENT, "config_set_gradient_exchange: 0 auto, 1 push, 2 pull");
+  C(h)->grad_exchange = mode;
   return FFEMB_OK;
 }
 extern "C" int ffemb_config_set_exchange_engine(ffemb_config_t h, int force) {
@@ -433,6 +444,14 @@ namespace ffemb {
 
 static size_t up256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+static void x_mark(Model *m, const char *name, cudaStream_t s) {
+  if (!m->x.trace || m->x.marks.size() >= 20000) return;
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, s);
+  m->x.marks.emplace_back(name, e);
+}
+
 // Launch groups of the sharded mode: this rank's sharded tables, or the
 // replicated ones, by (out_dim, aggr).
 struct XGroup {
@@ -478,7 +497,7 @@ static int x_lookups(Model *m, const XGroup &g, XMode mode, std::vector<ffemb_lo
       l.weight = op->W;
       l.indices = idx;
       l.num_indices = (int64_t)m->cfg.batch_size * L;
-      l.col = mode == kXFwd ? op->gcol : op->scol;
+      l.col = (mode == kXFwd || x.pull) ? op->gcol : op->scol;
     } else {
       l.weight = mode == kXRepFwd ? op->W : op->G;
       l.indices = idx + (int64_t)m->cfg.rank * x.Bs * L;
@@ -494,6 +513,16 @@ static ffemb_matrix_t x_matrix_out_peers(const Model *m) {  // forward: every ra
   ffemb_matrix_t mat;
   memset(&mat, 0, sizeof mat);
   for (int q = 0; q < m->world; ++q) mat.base[q] = (float *)(m->x.peer[q] + m->x.off_out);
+  mat.num_parts = m->world;
+  mat.rows_per_part = m->x.Bs;
+  mat.ld = m->x.ldx;
+  return mat;
+}
+
+static ffemb_matrix_t x_matrix_grad_peers(const Model *m) {  // pull: every rank's [Bs][ldx] gradient
+  ffemb_matrix_t mat;
+  memset(&mat, 0, sizeof mat);
+  for (int q = 0; q < m->world; ++q) mat.base[q] = (float *)(m->x.peer[q] + m->x.off_grad);
   mat.num_parts = m->world;
   mat.rows_per_part = m->x.Bs;
   mat.ld = m->x.ldx;
@@ -541,8 +570,9 @@ static int x_backward_groups(Model *m, bool rep, bool sort, bool update, float l
     if (update) {
       // replicas: dense gradient of this rank's own samples, from its [Bs][ldx]
       // gradient matrix; sharded: the whole batch's gradient in the staging matrix
-      ffemb_matrix_t mat = rep ? x_matrix_local(m, x.off_grad, x.Bs, x.ldx)
-                               : x_matrix_local(m, x.off_stage, batch, x.stage_ld[m->cfg.rank]);
+      ffemb_matrix_t mat = rep      ? x_matrix_local(m, x.off_grad, x.Bs, x.ldx)
+                           : x.pull ? x_matrix_grad_peers(m)
+                                    : x_matrix_local(m, x.off_stage, batch, x.stage_ld[m->cfg.rank]);
       if (int rc = ffemb_embed_sgd_update(lk.data(), (int)lk.size(), batch, g.D, (enum AggrMode)g.aggr, &mat, lr,
                                           ws + off, need, s))
         return rc;
@@ -576,15 +606,27 @@ static int x_forward(Model *m) {
   m->presorted = false;
   const bool presort = m->presort && m->opt;
   std::vector<ffemb_lookup_t> lk;
+  x_mark(m, "fwd_begin", m->stream);
   FFEMB_CUDA_OK(cudaEventRecord(m->ev_inputs, m->stream));
   // The key sorts of the coming backward need only the indices: they go first,
   // on their own streams, and run under the NVLink-bound gather.
-  if (presort && x.n_owned) {
+  // (Push mode sorts the sharded tables' keys in backward() instead, under the
+  // NVLink-bound gradient push: beside the gather the latency-bound sort ran
+  // 2-3x slower than alone and ended up as the forward's critical path.)
+  const bool presort_owned = presort && x.n_owned && x.pull;
+  if (presort_owned) {
     FFEMB_CUDA_OK(cudaStreamWaitEvent(m->side, m->ev_inputs, 0));
     if (int rc = x_backward_groups(m, false, true, false, 0.f, m->side)) return rc;
     FFEMB_CUDA_OK(cudaEventRecord(m->ev_sorted, m->side));
+    x_mark(m, "  (side) sharded tables' keys sorted", m->side);
   }
   if (x.n_rep) {
+    if (presort) {
+      FFEMB_CUDA_OK(cudaStreamWaitEvent(x.rep_side, m->ev_inputs, 0));
+      if (int rc = x_backward_groups(m, true, true, false, 0.f, x.rep_side)) return rc;
+      FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_sorted, x.rep_side));
+      x_mark(m, "  (rep side) replicas' keys sorted", x.rep_side);
+    }
     // replicated tables: this rank's own samples, straight into its own slice;
     // local traffic only, so it runs beside the sharded tables' gather
     FFEMB_CUDA_OK(cudaStreamWaitEvent(x.rep_stream, m->ev_inputs, 0));
@@ -596,10 +638,7 @@ static int x_forward(Model *m) {
         return rc;
     }
     FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_fwd, x.rep_stream));
-    if (presort) {
-      if (int rc = x_backward_groups(m, true, true, false, 0.f, x.rep_stream)) return rc;
-      FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_sorted, x.rep_stream));
-    }
+    x_mark(m, "  (rep) replicas gathered", x.rep_stream);
   }
   // sharded tables: the whole batch, every pooled row stored straight into the
   // consuming rank's [Bs][ldx] matrix over NVLink
@@ -612,17 +651,20 @@ static int x_forward(Model *m) {
         return rc;
     }
   }
+  x_mark(m, "sharded gather + remote stores done", m->stream);
   if (int rc = x_barrier(m, 0, m->stream)) return rc;  // every rank's rows have landed
+  x_mark(m, "forward barrier passed", m->stream);
   // join the forks: one timeline for the caller (and for a stream capture)
   if (x.n_rep) {
     FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, x.ev_rep_fwd, 0));
     if (presort) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, x.ev_rep_sorted, 0));
   }
-  if (presort && x.n_owned) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, m->ev_sorted, 0));
+  if (presort_owned) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, m->ev_sorted, 0));
   if (presort) {
     m->presort_sig = x_signature(m);
     m->presorted = true;
   }
+  x_mark(m, "forward end (forks joined)", m->stream);
   return FFEMB_OK;
 }
 
@@ -631,21 +673,34 @@ static int x_backward(Model *m) {
   if (int rc = x_require_connected(m, "backward")) return rc;
   const bool presorted = m->presorted && m->presort_sig == x_signature(m);
   m->presorted = false;
+  x_mark(m, "bwd_begin", m->stream);
   FFEMB_CUDA_OK(cudaEventRecord(x.ev_grads, m->stream));  // this rank's gradient matrix is complete
   if (x.n_rep) {
     // replicas (the reference's data-parallel embedding): dense gradient of
     // this rank's own samples -- the segment-reduce kernel with lr = -1 into a
     // zeroed G; update() sums the replicas and applies the step
     FFEMB_CUDA_OK(cudaStreamWaitEvent(x.rep_stream, x.ev_grads, 0));
+    // (a sort started by forward() was joined into the model stream there, so
+    // ev_grads already orders this branch after it)
     FFEMB_CUDA_OK(cudaMemsetAsync(x.buf + x.off_repG, 0, (size_t)x.rep_count * 4, x.rep_stream));
     if (int rc = x_backward_groups(m, true, !presorted, true, -1.0f, x.rep_stream)) return rc;
+    x_mark(m, "  (rep) own samples reduced into the dense replica gradient", x.rep_stream);
     x.rep_pending = true;
   }
-  if (!presorted && x.n_owned)
+  const bool fork_sort = x.n_owned && !x.pull && m->presort;
+  if (fork_sort) {  // the sharded tables' key sort runs under the gradient push
+    FFEMB_CUDA_OK(cudaStreamWaitEvent(m->side, x.ev_grads, 0));
+    if (int rc = x_backward_groups(m, false, true, false, 0.f, m->side)) return rc;
+    FFEMB_CUDA_OK(cudaEventRecord(m->ev_sorted, m->side));
+    x_mark(m, "  (side) sharded tables' keys sorted", m->side);
+  } else if (x.n_owned && !(presorted && x.pull)) {
     if (int rc = x_backward_groups(m, false, true, false, 0.f, m->stream)) return rc;
-  // gradient exchange as a push: every sharded table's column block of this
-  // rank's gradient goes to its owner's staging matrix, rows [rank*Bs, ..)
-  {
+  }
+  // gradient exchange.  Push: every sharded table's column block of this
+  // rank's gradient goes to its owner's staging matrix, rows [rank*Bs, ..), and
+  // the update then reads local memory.  Pull: nothing moves here; after the
+  // barrier the update kernel loads gradient rows from the peers' matrices.
+  if (!x.pull) {
     std::vector<int> dims;
     for (auto &op : m->ops)
       if (!op->replicated && std::find(dims.begin(), dims.end(), op->D) == dims.end()) dims.push_back(op->D);
@@ -665,7 +720,10 @@ static int x_backward(Model *m) {
         return rc;
     }
   }
+  x_mark(m, "gradient push done", m->stream);
   if (int rc = x_barrier(m, 0, m->stream)) return rc;  // the blocks have landed in the owners' staging
+  x_mark(m, "backward barrier passed", m->stream);
+  if (fork_sort) FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, m->ev_sorted, 0));  // join: one timeline
   return FFEMB_OK;
 }
 
@@ -674,6 +732,11 @@ static int x_update(Model *m) {
   const float lr = (float)m->opt->lr;
   if (x.n_owned)
     if (int rc = x_backward_groups(m, false, false, true, lr, m->stream)) return rc;
+  x_mark(m, "sharded tables updated", m->stream);
+  // pull: the peers have read this rank's gradient matrix inside their update;
+  // nobody may overwrite it (the next batch's gradients) before they are done
+  if (x.pull)
+    if (int rc = x_barrier(m, 0, m->stream)) return rc;
   if (x.rep_pending) {
     float *W[kMaxParts];
     const float *G[kMaxParts];
@@ -682,12 +745,16 @@ static int x_update(Model *m) {
       G[q] = (const float *)(x.peer[q] + x.off_repG);
     }
     if (int rc = x_barrier(m, 1, x.rep_stream)) return rc;  // every rank's replica gradient is complete
+    x_mark(m, "  (rep) replica barrier 1 passed", x.rep_stream);
     if (int rc = ffemb_replica_reduce_update(W, G, x.rep_count, m->cfg.rank, m->world, lr, x.rep_stream)) return rc;
+    x_mark(m, "  (rep) replicas summed, stepped, written to every rank", x.rep_stream);
     if (int rc = x_barrier(m, 1, x.rep_stream)) return rc;  // every copy of the tables is written
+    x_mark(m, "  (rep) replica barrier 2 passed", x.rep_stream);
     FFEMB_CUDA_OK(cudaEventRecord(x.ev_rep_done, x.rep_stream));
     FFEMB_CUDA_OK(cudaStreamWaitEvent(m->stream, x.ev_rep_done, 0));
     x.rep_pending = false;
   }
+  x_mark(m, "step end", m->stream);
   return FFEMB_OK;
 }
 
@@ -753,7 +820,8 @@ static int x_compile(Model *m) {
   x.off_grad = take((size_t)x.Bs * x.ldx * 4);
   x.off_repW = take((size_t)x.rep_count * 4);
   x.off_repG = take((size_t)x.rep_count * 4);
-  x.off_stage = take(x.n_owned ? (size_t)B * x.stage_ld[rank] * 4 : 0);
+  x.pull = m->cfg.grad_exchange == 2 || (m->cfg.grad_exchange == 0 && N == 2);
+  x.off_stage = take(x.n_owned && !x.pull ? (size_t)B * x.stage_ld[rank] * 4 : 0);
   x.bytes = off;
   FFEMB_CUDA_OK(cudaMalloc((void **)&x.buf, x.bytes));
   FFEMB_CUDA_OK(cudaMemsetAsync(x.buf, 0, x.bytes, m->stream));
@@ -797,7 +865,13 @@ static int x_compile(Model *m) {
   if (x.n_rep) {
     x.rep_ws_bytes = ffemb_embed_backward_workspace_bytes(rlookups, rentries, rmax_d) + ((size_t)(x.n_rep + 1) << 20);
     FFEMB_CUDA_OK(cudaMalloc(&x.rep_ws, x.rep_ws_bytes));
-    FFEMB_CUDA_OK(cudaStreamCreateWithFlags(&x.rep_stream, cudaStreamNonBlocking));
+    // The replicas' branch is a chain of small kernels, barriers and one small
+    // collective: at high priority its blocks are dispatched as slots free up
+    // instead of queueing behind the bulk kernels' grids.
+    int plo = 0, phi = 0;
+    FFEMB_CUDA_OK(cudaDeviceGetStreamPriorityRange(&plo, &phi));
+    FFEMB_CUDA_OK(cudaStreamCreateWithPriority(&x.rep_stream, cudaStreamNonBlocking, phi));
+    FFEMB_CUDA_OK(cudaStreamCreateWithPriority(&x.rep_side, cudaStreamNonBlocking, phi));
     FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_rep_fwd, cudaEventDisableTiming));
     FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_rep_sorted, cudaEventDisableTiming));
     FFEMB_CUDA_OK(cudaEventCreateWithFlags(&x.ev_rep_done, cudaEventDisableTiming));
@@ -817,6 +891,7 @@ static void x_destroy(Model *m) {
   if (x.buf) cudaFree(x.buf);
   if (x.rep_ws) cudaFree(x.rep_ws);
   if (x.rep_stream) cudaStreamDestroy(x.rep_stream);
+  if (x.rep_side) cudaStreamDestroy(x.rep_side);
   for (cudaEvent_t e : {x.ev_rep_fwd, x.ev_rep_sorted, x.ev_grads, x.ev_rep_done})
     if (e) cudaEventDestroy(e);
 }
@@ -827,6 +902,66 @@ using namespace ffemb;
 
 // ---- Sharded mode: connecting the ranks --------------------------------------
 extern "C" int ffemb_model_is_sharded(ffemb_model_t h) { return M(h) && M(h)->x.on ? 1 : 0; }
+
+// Development aid (sharded mode): timed events at the phase boundaries of the
+// steps that follow; the report gives, per mark, the mean time since the
+// step's forward began.  Not for use under stream capture.
+extern "C" int ffemb_model_trace(ffemb_model_t h, int enable) {
+  Model *m = M(h);
+  if (!m || !m->x.on) return fail(FFEMB_ERR_INVALID_ARGUMENT, "trace: not a sharded model");
+  m->x.trace = enable != 0;
+  return FFEMB_OK;
+}
+
+extern "C" size_t ffemb_model_trace_report(ffemb_model_t h, char *buf, size_t cap) {
+  Model *m = M(h);
+  if (!m || !m->x.on) return 0;
+  cudaSetDevice(m->device);
+  cudaDeviceSynchronize();
+  std::vector<std::string> names;
+  std::vector<double> sum;
+  std::vector<int> cnt;
+  cudaEvent_t begin = nullptr;
+  size_t k = 0;
+  int steps = 0;
+  for (auto &mk : m->x.marks) {
+    if (!strcmp(mk.first, "fwd_begin")) {
+      begin = mk.second;
+      k = 0;
+      ++steps;
+    }
+    if (begin) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, begin, mk.second);
+      if (k >= names.size()) {
+        names.push_back(mk.first);
+        sum.push_back(0.0);
+        cnt.push_back(0);
+      }
+      if (names[k] == mk.first) {
+        sum[k] += ms * 1e3;
+        ++cnt[k];
+      }
+      ++k;
+    }
+  }
+  std::string out = "rank " + std::to_string(m->cfg.rank) + " (" + std::to_string(m->x.n_owned) + " sharded, " +
+                    std::to_string(m->x.n_rep) + " replicated tables), " + std::to_string(steps) +
+                    " steps, mean us since the step's forward began:\n";
+  char line[256];
+  for (size_t i = 0; i < names.size(); ++i) {
+    snprintf(line, sizeof line, "  %8.1f  %s\n", cnt[i] ? sum[i] / cnt[i] : 0.0, names[i].c_str());
+    out += line;
+  }
+  if (buf && cap) {  // a sizing call (buf == NULL) keeps the record
+    const size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+    for (auto &mk : m->x.marks) cudaEventDestroy(mk.second);
+    m->x.marks.clear();
+  }
+  return out.size() + 1;
+}
 
 extern "C" int ffemb_model_get_exchange_handle(ffemb_model_t h, uint8_t handle[64]) {
   Model *m = M(h);

@@ -317,6 +317,14 @@ int ffemb_config_import_strategy_file(ffemb_config_t handle, const char *path);
  * break-even batch / ranks.  Without a strategy the remaining sharded tables
  * are dealt round-robin, in table order, over the ranks. */
 int ffemb_config_set_replicate_below(ffemb_config_t handle, int64_t rows);
+/* How the upstream gradients reach the tables' owners.  1 push: one kernel
+ * stores every table's block of a rank's gradient into its owner's staging
+ * matrix and the update reads local memory; 2 pull: the update kernel loads
+ * gradient rows straight from the producing ranks' matrices (no staging
+ * pass, but remote loads reach roughly half the NVLink rate of remote
+ * stores); 0 (default): pull with two ranks, push from three up -- where each
+ * measured faster. */
+int ffemb_config_set_gradient_exchange(ffemb_config_t handle, int mode);
 /* Run the sharded engine (exchange buffer, barriers, staging) even with one
  * rank.  For tests on a single GPU. */
 int ffemb_config_set_exchange_engine(ffemb_config_t handle, int force);
@@ -391,6 +399,13 @@ int ffemb_model_connect_peers(ffemb_model_t handle, const uint8_t *handles, int 
 /* This rank's [batch/ranks][ld] output (grad = false) or gradient matrix. */
 int ffemb_model_get_exchange_matrix(ffemb_model_t handle, bool grad, float **ptr,
                                     int64_t *ld, int *rows);
+
+/* Development aid, sharded mode: record timed events at the phase boundaries
+ * of the following steps (not under stream capture); the report lists, per
+ * boundary, the mean time since the step's forward began, and clears the
+ * record.  Returns the size the text needs. */
+int ffemb_model_trace(ffemb_model_t handle, int enable);
+size_t ffemb_model_trace_report(ffemb_model_t handle, char *buf, size_t cap);
 
 /* flexflow_model_init_layers (:98-100) -- EMBED_INIT_TASK is a no-op in the
  * reference too (src/ops/embedding.cu:137-144). */

@@ -32,7 +32,7 @@ def _inputs(seed):
     return idx, g
 
 
-def _run_rank(rank, world, replicate_below, owners, seed, force_engine=False, group=None):
+def _run_rank(rank, world, replicate_below, owners, seed, force_engine=False, group=None, gx="auto"):
     import dlrm_flexflow_b200 as ff
     from oracle import oracle as O
     T, Bs = len(ROWS), B // world
@@ -41,6 +41,7 @@ def _run_rank(rank, world, replicate_below, owners, seed, force_engine=False, gr
     cfg.set_workers_per_node(world)
     cfg.set_rank(rank, rank if world > 1 else -1)
     cfg.set_replicate_below(replicate_below)
+    cfg.set_gradient_exchange(gx)
     if force_engine:
         cfg.set_exchange_engine(True)
     m = ff.FFModel(cfg)
@@ -115,11 +116,12 @@ def _run_rank(rank, world, replicate_below, owners, seed, force_engine=False, gr
     m.close()
 
 
+@pytest.mark.parametrize("gx", ["push", "pull"])
 @pytest.mark.parametrize("replicate_below", [0, 500])
-def test_world1_engine(replicate_below):
+def test_world1_engine(replicate_below, gx):
     if not torch.cuda.is_available():
         pytest.fail("needs a CUDA device")
-    _run_rank(0, 1, replicate_below, None, seed=3, force_engine=True)
+    _run_rank(0, 1, replicate_below, None, seed=3, force_engine=True, gx=gx)
 
 
 def _free_port():
@@ -130,28 +132,30 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, replicate_below, owners, seed):
+def _worker(rank, world, port, replicate_below, owners, seed, gx):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        _run_rank(rank, world, replicate_below, owners, seed)
+        _run_rank(rank, world, replicate_below, owners, seed, gx=gx)
         dist.barrier()
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("replicate_below,owners", [
-    (0, None),                          # everything sharded, round-robin t % N (dlrm_strategy.cc:252-256)
-    (500, None),                        # three small tables replicated, the rest dealt round-robin
-    (0, [1, 1, 1, 0, 1, 1, 1]),         # a strategy with very uneven owners (folded % N)
-    (2000, [3, 5, 0, 7, 6, 2, 1]),      # replicas + a strategy for the sharded remainder
+@pytest.mark.parametrize("replicate_below,owners,gx", [
+    (0, None, "auto"),                          # everything sharded, round-robin t % N (dlrm_strategy.cc:252-256)
+    (500, None, "push"),                        # three small tables replicated, the rest dealt round-robin
+    (500, None, "pull"),
+    (0, [1, 1, 1, 0, 1, 1, 1], "push"),         # a strategy with very uneven owners (folded % N)
+    (2000, [3, 5, 0, 7, 6, 2, 1], "auto"),      # replicas + a strategy for the sharded remainder
+    (0, [1, 1, 1, 0, 1, 1, 1], "pull"),
 ])
-def test_sharded_model_matches_oracle(world, replicate_below, owners):
+def test_sharded_model_matches_oracle(world, replicate_below, owners, gx):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
     import torch.multiprocessing as mp
-    mp.spawn(_worker, args=(world, _free_port(), replicate_below, owners, 40 + world), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), replicate_below, owners, 40 + world, gx), nprocs=world, join=True)
