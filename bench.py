@@ -24,7 +24,8 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "DLRM embedding-bag samples/sec fwd+bwd"
-CPU_KEYS = ("value", "unit", "cores", "kind", "sample", "value_single_thread", "host_cpus", "cpu_model")
+CPU_KEYS = ("value", "unit", "cores", "kind", "sample", "value_single_thread", "host_cpus", "cpu_model", "row_cap",
+            "row_cap_source", "table_bytes_run")
 UNIT = "samples/s"
 
 
@@ -42,11 +43,17 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-row-cap", type=int, default=2_000_000)
+    ap.add_argument("--cpu-row-cap", type=int, default=0,
+                    help="CPU legs: cap every table at this many rows; 0 = the largest cap (at most 8 M rows, which "
+                         "bounds the set-up time) whose tables + gradient scratch fit in 40 %% of the free host RAM")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N>1: fused peer-memory exchange inside the kernels, or NCCL all-to-all")
-    ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balance"])
+    ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balance", "plan"],
+                    help="N>1: owners of the sharded tables.  round_robin: the reference's rule (in table order over "
+                         "the sharded tables); balance: ffemb_placement_balance on lookups; plan: "
+                         "ffemb_placement_plan decides shard-or-replicate per table from its step cost model "
+                         "(overrides --replicate)")
     ap.add_argument("--replicate", default="auto",
                     help="N>1: keep tables with fewer rows than this on every rank (data-parallel, gradient "
                          "all-reduce) instead of sharding them; 'auto' = batch/N (the break-even of SURVEY 7), "
@@ -172,9 +179,12 @@ def cpu_reference_run(w, steps, warmup, row_cap, lr):
 
     D, B, L, aggr = w["dim"], w["batch"], w["bag"], w["aggr"]
     avail = psutil.virtual_memory().available
+    cap_source = "--cpu-row-cap"
+    if row_cap <= 0:      # the largest that fits, bounded so that set-up stays within seconds
+        row_cap, cap_source = 8_000_000, "largest cap <= 8 M rows fitting 40 % of free host RAM"
     rows = [min(r, row_cap) for r in w["rows"]]
     while sum(rows) * D * 4 * 2 > 0.4 * avail and row_cap > 1000:   # tables + gradient scratch
-        row_cap //= 2
+        row_cap = row_cap * 3 // 4
         rows = [min(r, row_cap) for r in w["rows"]]
     T = len(rows)
     cores = min(os.cpu_count() or 1, T)
@@ -239,7 +249,8 @@ def cpu_reference_run(w, steps, warmup, row_cap, lr):
                  cores))
     return {"value": B / dt, "unit": UNIT, "cores": cores, "kind": "reference" if use_ref else "port",
             "sample": sample, "ms_per_step": dt * 1e3, "value_single_thread": B / dt1,
-            "host_cpus": os.cpu_count(), "cpu_model": cpu_model}
+            "host_cpus": os.cpu_count(), "cpu_model": cpu_model, "row_cap": row_cap, "row_cap_source": cap_source,
+            "table_bytes_run": sum(rows) * D * 4, "host_ram_available": avail}
 
 
 def run_reference_arm(args, w):
@@ -252,6 +263,11 @@ def run_reference_arm(args, w):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"],
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(args, w, 1),
+        # config names the workload (the same keys as our arm's line); what this arm really ran:
+        "reference_arm_sample": {"row_cap": cb["row_cap"], "row_cap_source": cb["row_cap_source"],
+                                 "table_bytes_run": cb["table_bytes_run"],
+                                 "table_bytes_of_the_workload": sum(w["rows"]) * w["dim"] * 4,
+                                 "threads": cb["cores"], "host_cpus": cb["host_cpus"]},
         "cpu_baseline": {k: cb[k] for k in CPU_KEYS},
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -302,11 +318,22 @@ def run_ours(args, w):
     cfg.set_batch_size(B)
     cfg.set_workers_per_node(world)
     cfg.set_rank(rank, local_rank)
+    plan_owner = None
+    if world > 1 and args.placement == "plan":
+        plan_owner, plan_us = ff.plan_placement(rows, [B * L] * T, D, B, world, 150 << 30)
+        rep_rows = [rows[t] for t in range(T) if plan_owner[t] < 0]
+        args.replicate = (max(rep_rows) + 1) if rep_rows else "off"      # the k smallest tables = a row threshold
     if world > 1:
         cfg.set_replicate_below({"auto": -1, "off": 0}.get(args.replicate, args.replicate))
         cfg.set_gradient_exchange(os.environ.get("FFEMB_BWD", "auto"))
     m = ff.FFModel(cfg)
     m.set_stream(stream.cuda_stream)
+    if plan_owner is not None:
+        st = ff.Strategy()
+        for t in range(T):
+            if plan_owner[t] >= 0 and rows[t] >= args.replicate:
+                st.add_op("embedding%d" % t, 0, [1, 1], [plan_owner[t]])
+        m.set_strategy(st)
     if world > 1 and args.placement == "balance":
         below = {"auto": B // world, "off": 0}.get(args.replicate, args.replicate)
         below = int(below)
@@ -625,8 +652,9 @@ def run_ours(args, w):
 
 
 def run_sharded(args, w, rank, world, local_rank):
-    """N > 1: tables sharded table-wise, one process per GPU, both exchanges
-    inside the step.  Time = max over ranks of the device time of K steps."""
+    """N > 1, --exchange nccl: the unfused baseline (local staging buffers, NCCL
+    all-to-all with uneven splits, strided pack/unpack), host-launched.
+    Time = max over ranks of the device time of K steps."""
     import torch
     import torch.distributed as dist
     from dlrm_flexflow_b200 import kernels, workloads
@@ -640,10 +668,7 @@ def run_sharded(args, w, rank, world, local_rank):
         owners = ff.balance_placement(rows, [B * L] * T, D, world, 150 << 30)
     plan = ShardPlan(rows, D, B, world, owners=owners,
                      replicate_below={"auto": "auto", "off": 0}.get(args.replicate, args.replicate))
-    sh = ShardedEmbeddingBags(plan, rank, L, aggr, args.lr, exchange=args.exchange,
-                              presort=os.environ.get("FFEMB_PRESORT", "1") == "1",
-                              barrier=os.environ.get("FFEMB_BARRIER", "peer"),
-                              backward_exchange=os.environ.get("FFEMB_BWD", "auto"))
+    sh = ShardedEmbeddingBags(plan, rank, L, aggr, args.lr, exchange="nccl")
     mine = plan.tables_of(rank)
     n_mine = len(mine)
     gen = torch.Generator(device="cuda")
@@ -688,41 +713,6 @@ def run_sharded(args, w, rank, world, local_rank):
 
     launches_per_step = None
     g_fwd = g_bwd = None
-    if args.graph and args.exchange == "p2p":
-        # forward (+ its exchange and barrier) and backward (+ barriers) as two
-        # CUDA graphs over fixed index buffers; the peer barrier keeps its count
-        # on the device, so replays stay in step across ranks.
-        flat_static = torch.empty_like(flats[0])
-        flat_static.copy_(flats[0])
-        idx_static = views(flat_static)
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for _ in range(2):
-                fwd(idx_static)
-                bwd(idx_static)
-        torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
-        dist.barrier()
-        l0 = kernels.kernel_launch_count()
-        g_fwd, g_bwd = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g_fwd):
-            fwd(idx_static)
-        with torch.cuda.graph(g_bwd):
-            bwd(idx_static)
-        launches_per_step = kernels.kernel_launch_count() - l0
-
-        def step(p, ev=None):      # noqa: F811
-            if ev:
-                ev[0].record()
-            flat_static.copy_(flats[p])
-            g_fwd.replay()
-            if ev:
-                ev[1].record()
-            g_bwd.replay()
-            if ev:
-                ev[2].record()
-
     for i in range(max(args.warmup, 3)):
         step(i % args.pool)
     sh.check_errors()
@@ -733,14 +723,9 @@ def run_sharded(args, w, rank, world, local_rank):
     launches0 = kernels.kernel_launch_count()
     dist.barrier()
     torch.cuda.synchronize()
-    if os.environ.get("FFEMB_TRACE") == "1" and launches_per_step is None:
-        sh.trace = []
     for i in range(K):
         step((args.warmup + i) % args.pool, evs[i])
     torch.cuda.synchronize()
-    if sh.trace is not None:
-        sys.stderr.write("TRACE rank %d (%d tables): %s\n" % (rank, len(mine), sh.trace_summary()))
-        sh.trace = None
     dist.barrier()
     launches = kernels.kernel_launch_count() - launches0
     if launches_per_step is not None:
@@ -775,7 +760,7 @@ def run_sharded(args, w, rank, world, local_rank):
         "phases": {"forward_and_exchange": {"ms": fwd_ms}, "exchange_sort_update": {"ms": bwd_ms}},
         "exchange": {"mode": args.exchange, "bytes_per_gpu_per_direction": xbytes,
                      "fwd_lower_bound_bus_gbs": xbytes / fwd_ms / 1e6, "nvlink_peak_gbs": 900.0,
-                     "backward": sh.bwd_mode if args.exchange == "p2p" else "all_to_all",
+                     "backward": "all_to_all",
                      "sharded_tables_per_rank": [len(plan.tables_of(r)) for r in range(world)],
                      "replicated_tables": len(plan.replicated), "replicate_below_rows": plan.replicate_below,
                      "replica_allreduce_bytes": plan.replica_allreduce_bytes(),

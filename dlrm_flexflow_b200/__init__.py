@@ -6,10 +6,10 @@ fails loudly if the extension cannot be built or loaded.
 """
 from .core import (AggrMode, DataType, OpType, FFConfig, FFModel, Tensor, Parameter, Op, Embedding,
                    SGDOptimizer, Initializer, UniformInitializer, ZeroInitializer, Strategy,
-                   round_robin_device, balance_placement)
+                   round_robin_device, balance_placement, plan_placement)
 from ._lib import FFEmbError, lib, library_path
 
 __all__ = ["AggrMode", "DataType", "OpType", "FFConfig", "FFModel", "Tensor", "Parameter", "Op",
            "Embedding", "SGDOptimizer", "Initializer", "UniformInitializer", "ZeroInitializer",
-           "Strategy", "round_robin_device", "balance_placement", "FFEmbError", "lib",
+           "Strategy", "round_robin_device", "balance_placement", "plan_placement", "FFEmbError", "lib",
            "library_path"]

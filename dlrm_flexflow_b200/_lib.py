@@ -181,6 +181,15 @@ SIGNATURES = {
     "ffemb_placement_balance": (_i, [C.POINTER(C.c_int64), C.POINTER(C.c_int64), _i, _i, _i, _i64, _ip]),
 }
 
+class CostModel(C.Structure):
+    """ffemb_cost_model_t"""
+    _fields_ = [("hbm_gbs", C.c_double), ("nvlink_gbs", C.c_double), ("hbm_passes", C.c_double),
+                ("replica_latency_us", C.c_double)]
+
+
+SIGNATURES["ffemb_placement_plan"] = (_i, [C.POINTER(C.c_int64), C.POINTER(C.c_int64), _i, _i, _i, _i, _i64,
+                                           C.POINTER(CostModel), _ip, C.POINTER(C.c_double)])
+
 _lib = None
 
 

@@ -406,6 +406,22 @@ def balance_placement(num_entries, lookups, out_dim, num_devices, bytes_capacity
     return list(owner)
 
 
+def plan_placement(num_entries, lookups, out_dim, batch, num_devices, bytes_capacity=0, cost=None):
+    """Shard / replicate decision and balanced owners from the step cost model
+    (ffemb_placement_plan).  Returns (owner list with -1 = replicated, modelled step in us)."""
+    T = len(num_entries)
+    ne = (C.c_int64 * T)(*num_entries)
+    lk = (C.c_int64 * T)(*lookups)
+    owner = (C.c_int * T)()
+    us = C.c_double()
+    cm = None
+    if cost is not None:
+        cm = _lib.CostModel(*cost)
+    check(lib().ffemb_placement_plan(ne, lk, T, out_dim, batch, num_devices, bytes_capacity,
+                                     C.byref(cm) if cm is not None else None, owner, C.byref(us)))
+    return list(owner), us.value
+
+
 # ---- FFModel ---------------------------------------------------------------------
 class FFModel(_Owned):
     def __init__(self, ffconfig):

@@ -367,3 +367,93 @@ extern "C" int ffemb_placement_balance(const int64_t *num_entries, const int64_t
   }
   return FFEMB_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Cost-aware placement with the replicate option.
+//
+// The reference cannot cost an embedding at all: Embedding::measure_compute_time
+// returns false (src/ops/embedding.cu:357-364), so its strategy search
+// (src/runtime/simulator.cc:200-275, link constants simulator.cu:27-29) never
+// moves the tables off the generator's round-robin.  This hook models one
+// step of the sharded engine per rank r:
+//   NVLink  2 * B*D*4*(N-1)/N bytes per sharded table r owns (pooled rows out,
+//           gradients in) + 2 * replica_bytes*(N-1)/N (sum + broadcast of the
+//           replicated tables' dense gradient / stepped rows)
+//   HBM     hbm_passes * D*4 bytes per lookup r processes (whole batch for its
+//           sharded tables, batch/N for every replicated one: row read, output
+//           write, gradient read, row read + write) + 3 * replica_bytes
+//   step    max(NVLink time, HBM time) [+ replica_latency_us if anything is
+//           replicated: the chain of small kernels, two barriers and the
+//           collective that the replicas add]
+// and picks, among "replicate the k smallest tables, balance the rest by
+// lookups" for k = 0..T, the k with the shortest modelled step.  Defaults are
+// this pool's measured rates (650 GB/s peer stores inside a kernel, 5.5 TB/s
+// gather/reduce kernels); with them the model lands within 15 % of the
+// measured C3 steps at 2 and 8 ranks, sharded and replicated.
+// ---------------------------------------------------------------------------
+extern "C" int ffemb_placement_plan(const int64_t *num_entries, const int64_t *lookups, int num_tables,
+                                    int out_dim, int batch, int num_devices, int64_t bytes_capacity,
+                                    const ffemb_cost_model_t *cost, int *owner, double *modelled_step_us) {
+  if (!num_entries || !lookups || !owner || num_tables < 0 || num_devices <= 0 || out_dim <= 0 || batch <= 0)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "placement_plan: bad arguments");
+  ffemb_cost_model_t c = {5500.0, 650.0, 5.0, 60.0};
+  if (cost) c = *cost;
+  if (c.hbm_gbs <= 0 || c.nvlink_gbs <= 0 || c.hbm_passes <= 0 || c.replica_latency_us < 0)
+    return fail(FFEMB_ERR_INVALID_ARGUMENT, "placement_plan: bad cost model");
+  const int T = num_tables, N = num_devices;
+  std::vector<int> by_rows(T);
+  std::iota(by_rows.begin(), by_rows.end(), 0);
+  std::stable_sort(by_rows.begin(), by_rows.end(), [&](int a, int b) { return num_entries[a] < num_entries[b]; });
+  const double row = (double)out_dim * 4.0;
+  const double frac = N > 1 ? (double)(N - 1) / N : 0.0;
+  double best = -1.0;
+  std::vector<int> best_owner(T, 0), cur(T, 0);
+  for (int k = 0; k <= (N > 1 ? T : 0); ++k) {
+    // the k smallest tables replicated, the rest balanced by lookups under the capacity
+    std::vector<int64_t> ne, lk;
+    std::vector<int> idx;
+    double rep_bytes = 0, rep_lookups = 0;
+    int64_t rep_cap = 0;
+    for (int i = 0; i < T; ++i) {
+      const int t = by_rows[i];
+      if (i < k) {
+        cur[t] = -1;
+        rep_bytes += (double)num_entries[t] * row;
+        rep_lookups += (double)lookups[t] / N;
+        rep_cap += num_entries[t] * (int64_t)out_dim * 8;  // table + dense gradient on every rank
+      } else {
+        idx.push_back(t);
+        ne.push_back(num_entries[t]);
+        lk.push_back(lookups[t]);
+      }
+    }
+    std::vector<int> own(idx.size(), 0);
+    if (bytes_capacity > 0 && rep_cap > bytes_capacity) continue;  // the replicas alone do not fit
+    if (!idx.empty()) {
+      const int64_t cap = bytes_capacity > 0 ? bytes_capacity - rep_cap : 0;
+      if (bytes_capacity > 0 && cap <= 0) continue;
+      if (ffemb_placement_balance(ne.data(), lk.data(), (int)idx.size(), out_dim, N, cap, own.data())) continue;
+    }
+    std::vector<double> nv(N, 0.0), hb(N, 0.0);
+    for (size_t i = 0; i < idx.size(); ++i) {
+      cur[idx[i]] = own[i];
+      nv[own[i]] += 2.0 * (double)batch * row * frac;
+      hb[own[i]] += c.hbm_passes * (double)lk[i] * row;
+    }
+    double step = 0.0;
+    for (int r = 0; r < N; ++r) {
+      const double t_nv = (nv[r] + 2.0 * rep_bytes * frac) / (c.nvlink_gbs * 1e3);          // us
+      const double t_hb = (hb[r] + c.hbm_passes * rep_lookups * row + 3.0 * rep_bytes) / (c.hbm_gbs * 1e3);
+      step = std::max(step, std::max(t_nv, t_hb));
+    }
+    if (k > 0) step += c.replica_latency_us;
+    if (best < 0 || step < best) {
+      best = step;
+      best_owner = cur;
+    }
+  }
+  if (best < 0) return fail(FFEMB_ERR_INVALID_ARGUMENT, "placement_plan: the tables do not fit the devices");
+  for (int t = 0; t < T; ++t) owner[t] = best_owner[t];
+  if (modelled_step_us) *modelled_step_us = best;
+  return FFEMB_OK;
+}

@@ -573,6 +573,26 @@ int ffemb_strategy_device_for_table(ffemb_strategy_t handle, int table_index,
 int ffemb_placement_balance(const int64_t *num_entries, const int64_t *lookups,
                             int num_tables, int out_dim, int num_devices,
                             int64_t bytes_capacity, int *owner);
+/* Cost-aware placement WITH the replicate option (the reference's
+ * simulator cannot cost an embedding: src/ops/embedding.cu:357-364,
+ * src/runtime/simulator.cc:200-275).  Models a step of the sharded engine per
+ * rank -- NVLink bytes of the two exchanges and of the replicas' sum, HBM
+ * bytes of the gathers and updates -- and picks, among "replicate the k
+ * smallest tables, balance the rest by lookups", the k with the shortest
+ * modelled step.  owner[t] = rank, or -1 = keep table t on every rank.
+ * `lookups[t]`: lookups of table t per step over the whole batch.  cost ==
+ * NULL: this pool's measured B200 rates.  modelled_step_us may be NULL. */
+typedef struct ffemb_cost_model_t {
+  double hbm_gbs;            /* rate the gather / reduce kernels sustain        */
+  double nvlink_gbs;         /* rate of peer stores issued from inside a kernel */
+  double hbm_passes;         /* row-sized HBM accesses per lookup (5: row read,
+                                output write, gradient read, row read + write)  */
+  double replica_latency_us; /* fixed cost of having any replicated table       */
+} ffemb_cost_model_t;
+int ffemb_placement_plan(const int64_t *num_entries, const int64_t *lookups,
+                         int num_tables, int out_dim, int batch, int num_devices,
+                         int64_t bytes_capacity, const ffemb_cost_model_t *cost,
+                         int *owner, double *modelled_step_us);
 /* Model-level: use this strategy at compile (overrides the config's file). */
 int ffemb_model_set_strategy(ffemb_model_t model, ffemb_strategy_t strategy);
 

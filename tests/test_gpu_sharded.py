@@ -1,7 +1,9 @@
-"""GPU tests of the table-wise sharded path.  World size 1 runs on any GPU box;
-the 2-rank NCCL runs need two GPUs (skipped otherwise) and check that both
-exchange modes give, on every rank, bit-identical forward outputs to the
-single-GPU / oracle result (SURVEY 8c rule 4) and tables within 1e-5."""
+"""GPU tests of the NCCL all-to-all baseline of the table-wise sharded path
+(dlrm_flexflow_b200/sharded.py; the peer-memory engine behind the operator API
+is covered by test_gpu_model_sharded.py).  World size 1 runs on any GPU box;
+the 2-rank runs need two GPUs (skipped otherwise) and check, on every rank,
+bit-identical forward outputs to the single-GPU / oracle result (SURVEY 8c rule
+4) and tables within 1e-5."""
 import os
 import socket
 import sys
@@ -25,12 +27,12 @@ def _problem(seed, T=5, D=64, B=256, L=2):
     return rows, D, B, L, idx, g
 
 
-def _run_rank(rank, world, exchange, owners, seed, lr=0.05, aggr=22, bwd="auto", replicate_below=0):
+def _run_rank(rank, world, exchange, owners, seed, lr=0.05, aggr=22, replicate_below=0):
     from oracle import oracle as O
     from dlrm_flexflow_b200.sharded import ShardPlan, ShardedEmbeddingBags
     rows, D, B, L, idx, g = _problem(seed)
     plan = ShardPlan(rows, D, B, world, owners=owners, replicate_below=replicate_below)
-    sh = ShardedEmbeddingBags(plan, rank, L, aggr, lr, exchange=exchange, backward_exchange=bwd)
+    sh = ShardedEmbeddingBags(plan, rank, L, aggr, lr, exchange=exchange)
     mine = plan.tables_of(rank)
     W0 = {t: sh.tables[i].cpu().numpy() for i, t in enumerate(mine)}
     rep = plan.replicated
@@ -73,7 +75,7 @@ def _run_rank(rank, world, exchange, owners, seed, lr=0.05, aggr=22, bwd="auto",
 def test_world1_sharded_wrapper():
     if not torch.cuda.is_available():
         pytest.fail("needs a CUDA device")
-    _run_rank(0, 1, "p2p", [0] * 5, seed=5)
+    _run_rank(0, 1, "nccl", [0] * 5, seed=5)
 
 
 def _free_port():
@@ -84,33 +86,37 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, exchange, owners, seed, bwd, replicate_below=0):
+def _worker(rank, world, port, exchange, owners, seed, replicate_below=0):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        _run_rank(rank, world, exchange, owners, seed, bwd=bwd, replicate_below=replicate_below)
+        _run_rank(rank, world, exchange, owners, seed, replicate_below=replicate_below)
         dist.barrier()
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange,bwd", [("p2p", "pull"), ("p2p", "push"), ("nccl", "auto")])
 @pytest.mark.parametrize("owners", [[0, 1, 0, 1, 0], [1, 1, 1, 1, 0]])
-def test_world2_nccl(exchange, bwd, owners):
+def test_world2_nccl(owners):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
-    mp.spawn(_worker, args=(2, _free_port(), exchange, owners, 9, bwd), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), "nccl", owners, 9), nprocs=2, join=True)
 
 
-@pytest.mark.parametrize("exchange,bwd", [("p2p", "pull"), ("p2p", "push"), ("nccl", "auto")])
-def test_world2_with_replicated_small_tables(exchange, bwd):
+def test_peer_memory_exchange_is_behind_the_operator_api():
+    from dlrm_flexflow_b200.sharded import ShardPlan, ShardedEmbeddingBags
+    with pytest.raises(ValueError):
+        ShardedEmbeddingBags(ShardPlan([10, 10], 16, 8, 1), 0, 1, 21, 0.1, exchange="p2p")
+
+
+def test_world2_with_replicated_small_tables():
     """Tables 0 and 1 (40 and 340 rows) are kept on both ranks (data-parallel,
     gradient replicas summed by all-reduce), the rest are sharded."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
-    mp.spawn(_worker, args=(2, _free_port(), exchange, [0, 1, 0, 1, 0], 11, bwd, 500), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), "nccl", [0, 1, 0, 1, 0], 11, 500), nprocs=2, join=True)

@@ -138,3 +138,36 @@ def test_shard_plan_layout_roundtrips(world, T, bs, rep_below, data):
             assert np.isnan(blk).all()                                 # replicated columns are produced locally
         else:
             assert blk.tobytes() == concat[:, t * D:(t + 1) * D].tobytes()
+
+
+def test_placement_plan_shard_or_replicate():
+    """ffemb_placement_plan: the cost model replicates only small
+    tables, never with one rank, never where the exchange is cheap relative to
+    the HBM work (multi-hot), keeps the sharded tables balanced and respects
+    the capacity."""
+    from dlrm_flexflow_b200.workloads import TERABYTE_ROWS as R, WORKLOADS
+    B = 65536
+    own, us1 = ff.plan_placement(R, [B] * 26, 128, B, 1)
+    assert own == [0] * 26
+    last = us1
+    for N in (2, 4, 8):
+        own, us = ff.plan_placement(R, [B] * 26, 128, B, N, 150 << 30)
+        rep = [t for t in range(26) if own[t] < 0]
+        assert rep and all(0 <= o < N for o in own if o >= 0)
+        assert max(R[t] for t in rep) < min(R[t] for t in range(26) if own[t] >= 0)      # the smallest ones
+        assert max(R[t] for t in rep) < B                                                 # never a big table
+        per = [sum(1 for o in own if o == r) for r in range(N)]
+        assert max(per) - min(per) <= 1                                                   # balanced by lookups
+        for r in range(N):      # capacity: sharded tables + every replica (table and dense gradient)
+            assert sum(R[t] for t in range(26) if own[t] == r) * 512 + sum(R[t] for t in rep) * 1024 <= 150 << 30
+        assert us < last        # more ranks, shorter modelled step
+        last = us
+    w = WORKLOADS["C4"]         # pooling 32: HBM work dwarfs the exchange, nothing to gain from replicas
+    own, _ = ff.plan_placement(w["rows"], [w["batch"] * w["bag"]] * 8, 128, w["batch"], 8)
+    assert sorted(own) == list(range(8))
+    # a cost model with a free network shards everything; with a very slow one it replicates more
+    own_fast, _ = ff.plan_placement(R, [B] * 26, 128, B, 8, cost=(5500.0, 1e9, 5.0, 60.0))
+    own_slow, _ = ff.plan_placement(R, [B] * 26, 128, B, 8, cost=(5500.0, 50.0, 5.0, 60.0))
+    assert sum(o < 0 for o in own_fast) == 0 < sum(o < 0 for o in own_slow)
+    with pytest.raises(ff.FFEmbError):
+        ff.plan_placement([10 ** 9] * 4, [B] * 4, 128, B, 2, bytes_capacity=1 << 30)       # nothing fits
