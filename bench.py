@@ -351,6 +351,8 @@ def run_ours(args, w):
         ins.append(x)
     m.compile(optimizer=ff.SGDOptimizer(m, args.lr))
     m.init_layers()
+    if os.environ.get("FFEMB_PRESORT", "1") == "0":      # development: the phases one after the other
+        m.set_presort(False)
     owner = [m.get_layer_by_id(t).get_device() for t in range(T)]      # -1: replicated on every rank
     held = [t for t in range(T) if owner[t] in (rank, -1)]              # tables whose indices this rank reads
     Bs = B // world

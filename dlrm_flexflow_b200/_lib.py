@@ -117,6 +117,7 @@ SIGNATURES = {
     "ffemb_model_update": (_i, [_H]),
     "ffemb_model_sync": (_i, [_H]),
     "ffemb_model_set_stream": (_i, [_H, _vp]),
+    "ffemb_model_set_presort": (_i, [_H, _b]),
     "ffemb_model_get_num_layers": (_i, [_H]),
     "ffemb_model_get_layer_by_id": (_H, [_H, _i]),
     "ffemb_model_set_strategy": (_i, [_H, _H]),

@@ -476,6 +476,9 @@ class FFModel(_Owned):
         self._keep.append(strategy)
         check(lib().ffemb_model_set_strategy(self.handle, strategy.handle))
 
+    def set_presort(self, enable=True):
+        check(lib().ffemb_model_set_presort(self.handle, bool(enable)))
+
     def set_stream(self, cuda_stream_ptr):
         check(lib().ffemb_model_set_stream(self.handle, cuda_stream_ptr))
 

@@ -431,6 +431,12 @@ extern "C" int ffemb_model_set_strategy(ffemb_model_t h, ffemb_strategy_t s) {
   return FFEMB_OK;
 }
 
+extern "C" int ffemb_model_set_presort(ffemb_model_t h, bool enable) {
+  if (!M(h)) return fail(FFEMB_ERR_INVALID_ARGUMENT, "set_presort: NULL model");
+  M(h)->presort = enable;
+  return FFEMB_OK;
+}
+
 extern "C" int ffemb_model_set_stream(ffemb_model_t h, void *stream) {
   if (!M(h)) return fail(FFEMB_ERR_INVALID_ARGUMENT, "set_stream: NULL model");
   M(h)->stream = (cudaStream_t)stream;
@@ -1389,9 +1395,14 @@ extern "C" int ffemb_model_load_batch_async(ffemb_model_t h, const int64_t *cons
     }
     FFEMB_CUDA_OK(cudaMemcpyAsync(dst + first, src + first, cnt * sizeof(int64_t), cudaMemcpyHostToDevice, p->s_in));
   }
-  if (out_grad)
-    FFEMB_CUDA_OK(cudaMemcpy2DAsync(p->grad[s], p->ld * sizeof(float), out_grad, p->width * sizeof(float),
-                                    p->width * sizeof(float), p->rows, cudaMemcpyHostToDevice, p->s_in));
+  if (out_grad) {
+    if (p->ld == p->width)  // contiguous on both sides: one linear copy runs at the full PCIe rate
+      FFEMB_CUDA_OK(cudaMemcpyAsync(p->grad[s], out_grad, (size_t)p->rows * p->width * sizeof(float),
+                                    cudaMemcpyHostToDevice, p->s_in));
+    else
+      FFEMB_CUDA_OK(cudaMemcpy2DAsync(p->grad[s], p->ld * sizeof(float), out_grad, p->width * sizeof(float),
+                                      p->width * sizeof(float), p->rows, cudaMemcpyHostToDevice, p->s_in));
+  }
   FFEMB_CUDA_OK(cudaEventRecord(p->ev_in[s], p->s_in));
   p->loaded[s] = true;
   p->next = s ^ 1;
@@ -1449,8 +1460,12 @@ extern "C" int ffemb_model_fetch_outputs_async(ffemb_model_t h, float *out_host)
                                   cudaMemcpyDeviceToDevice, m->stream));
   FFEMB_CUDA_OK(cudaEventRecord(p->ev_fwd[s], m->stream));
   FFEMB_CUDA_OK(cudaStreamWaitEvent(p->s_out, p->ev_fwd[s], 0));
-  FFEMB_CUDA_OK(cudaMemcpy2DAsync(out_host, p->width * sizeof(float), p->out[s], p->ld * sizeof(float),
-                                  p->width * sizeof(float), p->rows, cudaMemcpyDeviceToHost, p->s_out));
+  if (p->ld == p->width)
+    FFEMB_CUDA_OK(cudaMemcpyAsync(out_host, p->out[s], (size_t)p->rows * p->width * sizeof(float),
+                                  cudaMemcpyDeviceToHost, p->s_out));
+  else
+    FFEMB_CUDA_OK(cudaMemcpy2DAsync(out_host, p->width * sizeof(float), p->out[s], p->ld * sizeof(float),
+                                    p->width * sizeof(float), p->rows, cudaMemcpyDeviceToHost, p->s_out));
   FFEMB_CUDA_OK(cudaEventRecord(p->ev_out[s], p->s_out));
   p->out_rec[s] = true;
   p->prev_fetch = p->last_fetch;

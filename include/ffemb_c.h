@@ -423,6 +423,11 @@ int ffemb_model_update(ffemb_model_t handle);
 /* Blocks until the model's stream is idle, then reports (and clears) a
  * pending out-of-range-index error. */
 int ffemb_model_sync(ffemb_model_t handle);
+/* forward() of a model with an optimizer starts the coming backward's key
+ * sort on a side stream (it needs only the indices) so that it runs under the
+ * gather; `enable = false` leaves the sort to backward() (inference-style
+ * forward calls, measurements of the kernels in isolation).  Default: true. */
+int ffemb_model_set_presort(ffemb_model_t handle, bool enable);
 /* Use `stream` (a cudaStream_t) for all model work; NULL = default stream. */
 int ffemb_model_set_stream(ffemb_model_t handle, void *stream);
 
