@@ -32,7 +32,10 @@ namespace ffemb {
 // 0: CUB DeviceRadixSort (library); 1: the segmented per-table sort of ffemb_sort.cuh
 // (three launches per pass, through global memory); 2: the one-launch on-chip
 // cluster sort of ffemb_csort.cuh where every table's segment fits (<= 65536
-// lookups per table), else 1.  Launch groups with 2^32-1 rows or more: always 0.
+// lookups per table), else 0 -- for segments of half a million lookups (C4) the
+// library sort's 7 launches hide better under the gather than the 10 of the own
+// global sort (forward + sort 0.51 vs 0.61 ms).  Launch groups with 2^32-1 rows
+// or more: always 0.
 #ifndef FFEMB_DEFAULT_SORT
 #define FFEMB_DEFAULT_SORT 2
 #endif
@@ -639,7 +642,7 @@ static int sort_group(const ffemb_lookup_t *lookups, int T, int batch, const Wor
       return rc;
     if (done) return FFEMB_OK;
   }
-  if (sizeof(KeyT) == 4 && impl >= 1)
+  if (sizeof(KeyT) == 4 && impl == 1)
     return own_sort_group(lookups, T, batch, (uint32_t *)w.keys_a, (uint32_t *)w.keys_b, w.vals_a,
                           w.vals_b, (uint32_t *)w.sort_tmp, err, s);
   KeyParams kp;

@@ -145,9 +145,9 @@ int ffemb_embed_backward_sgd(const ffemb_lookup_t *lookups, int num_tables,
 /* Which key sort the backward uses (process-wide).
  *   2 (default): this library's one-launch on-chip sort (csrc/ffemb_csort.cuh):
  *      one thread-block cluster per table keeps the table's whole segment in
- *      distributed shared memory across its radix passes.  Used when every
- *      table of the launch has at most 65536 lookups and batch <= 65536;
- *      otherwise 1 is used.
+ *      shared memory across its radix passes.  Used when every table of the
+ *      launch has at most 65536 lookups and batch <= 65536; otherwise 0 is
+ *      used (measured faster than 1 on half-million-lookup segments).
  *   1: this library's segmented sort through global memory
  *      (csrc/ffemb_sort.cuh), every table's segment sorted by row number with
  *      only as many passes as that table's size needs.

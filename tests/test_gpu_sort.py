@@ -47,7 +47,7 @@ def _step(K, impl, Ws, idxs, g, aggr, B, offsets=None):
     ([700, 200000], 32, 16385, 1, 21),            # one lookup more than a CTA's slab: 2-CTA clusters
     ([5000, 123], 16, 8192, 8, 22),               # bags of 8: 65536 lookups per table
     ([150000000], 4, 4096, 1, 21),                # 28 key bits: 4 passes
-    ([900, 70000], 16, 8192, 9, 21),              # 73728 lookups per table: too big for a cluster -> impl 1
+    ([900, 70000], 16, 8192, 9, 21),              # 73728 lookups per table: too big for a cluster -> falls back
 ])
 @pytest.mark.parametrize("impl", [1, 2])
 def test_own_sort_gives_the_same_tables_bit_for_bit(K, rows, D, B, L, aggr, impl):
