@@ -4,9 +4,9 @@
 // by row inside each table's segment (ffemb_sort.cuh explains why).  When a
 // table's segment has at most 65536 lookups -- every DLRM shape with batch <=
 // 65536 and one-hot bags, and every shard of a bigger job -- one thread-block
-// CLUSTER of up to 4 CTAs sorts the table start to finish in a single launch:
-// CTA r owns slots [r*16384, (r+1)*16384) of the segment's current order and
-// keeps them in shared memory as (row u32, bag u16).
+// CLUSTER of up to 8 CTAs sorts the table start to finish in a single launch:
+// CTA r owns a slab of up to 16384 consecutive slots of the segment's current
+// order and keeps them in shared memory as (row u32, bag u16).
 //
 //   pass k   stable LSD radix pass on digit k (<= 9 bits; a table takes only
 //            ceil(bits(N_t) / 9) passes):
@@ -50,6 +50,12 @@ constexpr int kCsMaxBits = 9;
 constexpr int kCsRadix = 1 << kCsMaxBits;
 constexpr int kCsPerWarp = kCsSlab / kCsWarps;      // 1024 slots per warp
 constexpr int kCsPerThread = kCsSlab / kCsThreads;  // 32 slots per thread
+#ifndef FFEMB_CS_DSMEM
+#define FFEMB_CS_DSMEM 1
+#endif
+// between passes the digit runs move CTA to CTA through distributed shared
+// memory (1) or through L2 (0)
+constexpr bool kCsDsmem = FFEMB_CS_DSMEM != 0;
 constexpr size_t kCsSmemBytes = (size_t)2 * kCsSlab * 4      // rows: slab + reordered
                                 + (size_t)2 * kCsSlab * 2    // bags: slab + reordered
                                 + (size_t)kCsWarps * kCsRadix * 2  // per-warp digit counters
@@ -73,6 +79,7 @@ struct CsParams {
   uint32_t *keys_out;
   uint32_t *vals_out;
   uint2 *tmp;  // [n] (row, bag) records between passes
+  int slab_log2;  // slots per CTA in this launch = 1 << slab_log2 (<= kCsSlab)
   int B;
   int *err;
 };
@@ -117,8 +124,9 @@ __global__ void __maxnreg__(FFEMB_CS_MAXNREG) cluster_sort_kernel(const __grid_c
   const uint32_t n = tb.n;
   if (n == 0) return;  // the same decision in every CTA of the cluster
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
-  const uint32_t slab0 = r * (uint32_t)kCsSlab;
-  const uint32_t m = n > slab0 ? (n - slab0 < (uint32_t)kCsSlab ? n - slab0 : (uint32_t)kCsSlab) : 0u;
+  const uint32_t slab = 1u << p.slab_log2;
+  const uint32_t slab0 = r * slab;
+  const uint32_t m = n > slab0 ? (n - slab0 < slab ? n - slab0 : slab) : 0u;
   uint2 *const tmp = p.tmp + tb.pos_base;
   bool bad = false;
 
@@ -164,6 +172,7 @@ __global__ void __maxnreg__(FFEMB_CS_MAXNREG) cluster_sort_kernel(const __grid_c
       const int64_t *src = tb.idx + slab0;
 #pragma unroll
       for (int j0 = 0; j0 < kCsPerThread; j0 += 16) {
+        if ((uint32_t)j0 * kCsThreads >= m) break;  // uniform: short slabs stop early
         int64_t v[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
@@ -185,9 +194,10 @@ __global__ void __maxnreg__(FFEMB_CS_MAXNREG) cluster_sort_kernel(const __grid_c
           }
         }
       }
-    } else if (pass == 0 || C > 1) {
+    } else if (pass == 0 || (C > 1 && !kCsDsmem)) {
 #pragma unroll
       for (int j0 = 0; j0 < kCsPerThread; j0 += 16) {
+        if ((uint32_t)j0 * kCsThreads >= m) break;  // uniform: short slabs stop early
         uint2 v[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
@@ -331,8 +341,34 @@ __global__ void __maxnreg__(FFEMB_CS_MAXNREG) cluster_sort_kernel(const __grid_c
       continue;
     }
     // ---- copy every digit's run to its slots, coalesced ------------------------
+    if (kCsDsmem && !last) {
+      // The runs go straight into the slab (shared memory) of whichever CTA
+      // owns their slots: consecutive lanes hold consecutive slots of a run,
+      // so these are coalesced distributed-shared-memory stores.  Every CTA
+      // of the cluster must be done reading its slab first.
+      cluster.sync();
+#pragma unroll 8
+      for (int j = 0; j < kCsPerThread; ++j) {
+        if ((uint32_t)j * kCsThreads >= m) break;
+        const uint32_t e = (uint32_t)j * kCsThreads + tid;
+        if (e < m) {
+          const uint32_t row = s_rows2[e];
+          const uint32_t d = (row >> shift) & mask;
+          const uint32_t g = s_gbase[d] + (e - s_lbase[d]);
+          const unsigned dst = g >> p.slab_log2;
+          const uint32_t o = g & (slab - 1u);
+          cluster.map_shared_rank(s_rows, dst)[o] = row;
+          cluster.map_shared_rank(s_bags, dst)[o] = s_bags2[e];
+        }
+      }
+      CS_MARK(7);
+      cluster.sync();  // the next pass's slabs are complete; digit totals may be overwritten
+      CS_MARK(8);
+      continue;
+    }
 #pragma unroll 8
     for (int j = 0; j < kCsPerThread; ++j) {
+        if ((uint32_t)j * kCsThreads >= m) break;
       const uint32_t e = (uint32_t)j * kCsThreads + tid;
       if (e < m) {
         const uint32_t row = s_rows2[e];
@@ -396,8 +432,16 @@ inline int cluster_sort_group(const ffemb_lookup_t *lookups, int T, int batch, u
   cp.tmp = tmp;
   cp.B = batch;
   cp.err = err;
+  // Cluster size: what the largest segment needs, and beyond that as many CTAs
+  // per table (up to the portable 8) as keep the launch within about 64 CTAs --
+  // a rank that sorts two tables wants them spread over 16 SMs (the sort is
+  // latency-bound per CTA), a GPU that sorts 26 wants no more CTAs than needed.
   int C = 1;
   while ((int64_t)C * kCsSlab < max_n) C *= 2;
+  while (C < 8 && T * C * 2 <= 64) C *= 2;
+  int slab_log2 = 5;
+  while (((int64_t)C << slab_log2) < max_n) ++slab_log2;
+  cp.slab_log2 = slab_log2;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(T * C), 1, 1);
   cfg.blockDim = dim3(kCsThreads, 1, 1);

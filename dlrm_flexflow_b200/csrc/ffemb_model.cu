@@ -5,6 +5,7 @@
 // SGDOptimizer, Uniform/Zero initialisers.  Everything Legion did for this
 // path (regions, partitions, mapping) collapses to: which rank owns which
 // table (the placement hook), device buffers, one stream.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -106,6 +107,7 @@ struct Exchange {
   cudaEvent_t ev_rep_fwd = nullptr, ev_rep_sorted = nullptr, ev_grads = nullptr, ev_rep_done = nullptr;
   bool rep_pending = false;   // backward() left a replica gradient for update() to reduce
   bool pull = false;          // gradient exchange: the update kernel loads rows from the peers' matrices
+  bool sort_in_forward = false;  // sharded tables' key sort: under the gather (true) or under the push
   cudaStream_t rep_side = nullptr;  // high priority: the replicas' key sort
   // development aid: timed events at the phase boundaries of a step (all streams)
   bool trace = false;
@@ -619,7 +621,7 @@ static int x_forward(Model *m) {
   // (Push mode sorts the sharded tables' keys in backward() instead, under the
   // NVLink-bound gradient push: beside the gather the latency-bound sort ran
   // 2-3x slower than alone and ended up as the forward's critical path.)
-  const bool presort_owned = presort && x.n_owned && x.pull;
+  const bool presort_owned = presort && x.n_owned && x.sort_in_forward;
   if (presort_owned) {
     FFEMB_CUDA_OK(cudaStreamWaitEvent(m->side, m->ev_inputs, 0));
     if (int rc = x_backward_groups(m, false, true, false, 0.f, m->side)) return rc;
@@ -693,13 +695,13 @@ static int x_backward(Model *m) {
     x_mark(m, "  (rep) own samples reduced into the dense replica gradient", x.rep_stream);
     x.rep_pending = true;
   }
-  const bool fork_sort = x.n_owned && !x.pull && m->presort;
+  const bool fork_sort = x.n_owned && !x.sort_in_forward && m->presort;
   if (fork_sort) {  // the sharded tables' key sort runs under the gradient push
     FFEMB_CUDA_OK(cudaStreamWaitEvent(m->side, x.ev_grads, 0));
     if (int rc = x_backward_groups(m, false, true, false, 0.f, m->side)) return rc;
     FFEMB_CUDA_OK(cudaEventRecord(m->ev_sorted, m->side));
     x_mark(m, "  (side) sharded tables' keys sorted", m->side);
-  } else if (x.n_owned && !(presorted && x.pull)) {
+  } else if (x.n_owned && !(presorted && x.sort_in_forward)) {
     if (int rc = x_backward_groups(m, false, true, false, 0.f, m->stream)) return rc;
   }
   // gradient exchange.  Push: every sharded table's column block of this
@@ -827,6 +829,9 @@ static int x_compile(Model *m) {
   x.off_repW = take((size_t)x.rep_count * 4);
   x.off_repG = take((size_t)x.rep_count * 4);
   x.pull = m->cfg.grad_exchange == 2 || (m->cfg.grad_exchange == 0 && N == 2);
+  x.sort_in_forward = x.pull;  // pull has no push to hide the sort under
+  if (const char *e = getenv("FFEMB_SHARDED_SORT"))  // development switch: "fwd" / "bwd"
+    x.sort_in_forward = !strcmp(e, "fwd") || x.pull;
   x.off_stage = take(x.n_owned && !x.pull ? (size_t)B * x.stage_ld[rank] * 4 : 0);
   x.bytes = off;
   FFEMB_CUDA_OK(cudaMalloc((void **)&x.buf, x.bytes));
