@@ -17,6 +17,13 @@ update are libffemb.so, driven through the reference's own call sequence.
 The embedding outputs and their gradients live in one [batch, T*D] torch
 tensor that the library reads and writes in place (the Concat layout), so the
 "cat" interaction costs no copy.
+
+Under `torchrun --nproc-per-node N examples/dlrm_small.py -ll:gpu N [--import-strategy
+<file.pb>]` the same program runs sharded, as the reference's does under
+Legion with a strategy file (src/mapper/mapper.cc:282-286): the tables are
+placed table-wise by the library, every rank keeps batch / N samples of the
+dense part (data parallel, gradients averaged with an all-reduce) and reads
+its slice of all tables' outputs from the library's exchange matrix.
 """
 import argparse
 import os
@@ -52,7 +59,15 @@ def main(argv=None):
     ap.add_argument("--arch-mlp-bot", default="64-512-512-64")
     ap.add_argument("--arch-mlp-top", default="576-1024-1024-1024-1")
     ap.add_argument("--lr", type=float, default=0.01)
+    ap.add_argument("-ll:gpu", dest="gpus", type=int, default=1)
+    ap.add_argument("--import-strategy", "--import", dest="strategy", default=None)
     args = ap.parse_args(argv)
+    world, rank = args.gpus, int(os.environ.get("RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        if not dist.is_initialized():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
 
     assert torch.cuda.is_available(), "needs a CUDA device: the embedding path has no CPU fallback"
     dev = torch.device("cuda")
@@ -67,7 +82,12 @@ def main(argv=None):
     # ---- the model, built as the reference example builds it -------------------
     ffconfig = ff.FFConfig()
     ffconfig.set_batch_size(B)
+    ffconfig.set_workers_per_node(world)
+    ffconfig.set_rank(rank, torch.cuda.current_device())
+    if args.strategy:
+        ffconfig.import_strategy_file(args.strategy)
     ffmodel = ff.FFModel(ffconfig)
+    Bs = B // world                                        # samples of the dense part on this rank
     sparse_inputs = [ffmodel.create_tensor([B, L], ff.DataType.DT_INT64) for _ in range(T)]
     ly = []
     for i in range(T):
@@ -82,35 +102,47 @@ def main(argv=None):
     bot_mlp, top_mlp = mlp(bot).to(dev), mlp(top, sigmoid_layer=len(top) - 2).to(dev)
     dense_opt = torch.optim.SGD(list(bot_mlp.parameters()) + list(top_mlp.parameters()), lr=args.lr)
 
-    # z = cat(x, ly...): one [B, (T+1)*D] buffer; the library writes the T embedding blocks in place
-    z = torch.zeros((B, (T + 1) * D), device=dev)
-    gz = torch.zeros_like(z)
-    for i in range(T):
-        ly[i].attach_torch(z[:, (i + 1) * D:(i + 2) * D])
-        ly[i].attach_torch(gz[:, (i + 1) * D:(i + 2) * D], grad=True)
+    if world == 1:
+        # z = cat(x, ly...): one [B, (T+1)*D] buffer; the library writes the T embedding blocks in place
+        z = torch.zeros((B, (T + 1) * D), device=dev)
+        gz = torch.zeros_like(z)
+        for i in range(T):
+            ly[i].attach_torch(z[:, (i + 1) * D:(i + 2) * D])
+            ly[i].attach_torch(gz[:, (i + 1) * D:(i + 2) * D], grad=True)
+        emb_out, emb_grad = z[:, D:], gz[:, D:]
+    else:
+        # sharded: this rank's [B/N, T*D] slices of all tables' outputs / gradients (peer-mapped, library-owned)
+        emb_out, emb_grad = ffmodel.exchange_matrix(False), ffmodel.exchange_matrix(True)
 
     gen = torch.Generator(device="cuda")
-    gen.manual_seed(1)
-    dense_in = torch.rand((B, bot[0]), device=dev, generator=gen)
-    label = torch.rand((B, 1), device=dev, generator=gen)
+    gen.manual_seed(1)                                     # the same data on every rank; each takes its samples
+    dense_in = torch.rand((B, bot[0]), device=dev, generator=gen)[rank * Bs:(rank + 1) * Bs]
+    label = torch.rand((B, 1), device=dev, generator=gen)[rank * Bs:(rank + 1) * Bs]
     idx = [torch.randint(0, rows[i], (B, L), device=dev, generator=gen) for i in range(T)]   # rand() % N
     for i in range(T):
-        sparse_inputs[i].attach_torch(idx[i])
+        sparse_inputs[i].attach_torch(idx[i])              # a rank reads only what its tables need
+    dense_params = list(bot_mlp.parameters()) + list(top_mlp.parameters())
 
     def iteration():
-        ffmodel.forward()                                  # embeddings -> z[:, D:]
+        ffmodel.forward()                                  # embeddings -> this rank's samples of every table
         x = bot_mlp(dense_in)
-        emb = z[:, D:].detach().requires_grad_(True)       # the T embedding blocks, already side by side
+        emb = emb_out.detach().requires_grad_(True)        # the T embedding blocks, already side by side
         p = top_mlp(torch.cat([x, emb], dim=1))            # interact_features "cat" (dlrm.cc:49-65)
-        loss = torch.nn.functional.mse_loss(p, label)     # LOSS_MEAN_SQUARED_ERROR_AVG_REDUCE
+        loss = torch.nn.functional.mse_loss(p, label) / world   # LOSS_MEAN_SQUARED_ERROR_AVG_REDUCE over the batch
         dense_opt.zero_grad(set_to_none=True)
         ffmodel.zero_gradients()
         loss.backward()
-        gz[:, D:].copy_(emb.grad)                          # d loss / d embedding outputs
+        emb_grad.copy_(emb.grad)                           # d loss / d embedding outputs
         ffmodel.backward()
+        if world > 1:                                      # data-parallel dense part: sum of the ranks' gradients
+            for q in dense_params:
+                dist.all_reduce(q.grad)
         dense_opt.step()
         ffmodel.update()
-        return loss.detach()
+        total = loss.detach().clone()
+        if world > 1:
+            dist.all_reduce(total)
+        return total
 
     loss0 = float(iteration())                           # warm-up iteration (dlrm.cc:143-152)
     ffmodel.sync()
@@ -124,8 +156,11 @@ def main(argv=None):
     torch.cuda.synchronize()
     run_time = time.perf_counter() - ts
     n = B * args.iterations * args.epochs
-    print("loss: first %.6f last %.6f" % (loss0, float(loss)))
-    print("ELAPSED TIME = %.4fs, THROUGHPUT = %.2f samples/s" % (run_time, n / run_time))
+    if rank == 0:
+        print("loss: first %.6f last %.6f" % (loss0, float(loss)))
+        print("ELAPSED TIME = %.4fs, THROUGHPUT = %.2f samples/s" % (run_time, n / run_time))
+    if world > 1:
+        ffmodel.close()
     return loss0, float(loss)
 
 

@@ -44,6 +44,15 @@ def _run_rank(rank, world, replicate_below, owners, seed, force_engine=False, gr
     cfg.set_gradient_exchange(gx)
     if force_engine:
         cfg.set_exchange_engine(True)
+    if owners == "file":      # a strategy FILE written by the reference's generator rule: table i -> i % 8
+        import tempfile
+        path = os.path.join(tempfile.gettempdir(), "ffemb_strategy_%d_%d.pb" % (os.getpid(), rank))
+        ff.Strategy.dlrm_simple(8, len(ROWS)).save(path)
+        cfg.import_strategy_file(path)
+        owners = None
+        expect_owner = [t % 8 % world for t in range(len(ROWS))]
+    else:
+        expect_owner = None
     m = ff.FFModel(cfg)
     if owners is not None:
         s = ff.Strategy()
@@ -63,6 +72,8 @@ def _run_rank(rank, world, replicate_below, owners, seed, force_engine=False, gr
     assert replicated == [t for t, n in enumerate(ROWS) if n < replicate_below]
     if owners is not None:
         assert all(m.get_layer_by_id(t).get_device() == owners[t] % world for t in range(T) if t not in replicated)
+    if expect_owner is not None:
+        assert all(m.get_layer_by_id(t).get_device() == expect_owner[t] for t in range(T) if t not in replicated)
     idx, grads = _inputs(seed)
     W = []
     for t, n in enumerate(ROWS):      # every table's start is reproducible from its seed on any rank
@@ -124,6 +135,12 @@ def test_world1_engine(replicate_below, gx):
     _run_rank(0, 1, replicate_below, None, seed=3, force_engine=True, gx=gx)
 
 
+def test_world1_engine_with_strategy_file():
+    if not torch.cuda.is_available():
+        pytest.fail("needs a CUDA device")
+    _run_rank(0, 1, 0, "file", seed=4, force_engine=True)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -153,6 +170,7 @@ def _worker(rank, world, port, replicate_below, owners, seed, gx):
     (0, [1, 1, 1, 0, 1, 1, 1], "push"),         # a strategy with very uneven owners (folded % N)
     (2000, [3, 5, 0, 7, 6, 2, 1], "auto"),      # replicas + a strategy for the sharded remainder
     (0, [1, 1, 1, 0, 1, 1, 1], "pull"),
+    (500, "file", "auto"),                      # --import-strategy with the reference's 8-GPU generator rule
 ])
 def test_sharded_model_matches_oracle(world, replicate_below, owners, gx):
     if torch.cuda.device_count() < world:
