@@ -44,7 +44,7 @@ static uint64_t host_mix64(uint64_t z) {
 using namespace ffemb;
 
 extern "C" const char *ffemb_last_error(void) { return t_error.c_str(); }
-extern "C" const char *ffemb_version(void) { return "0.1.0"; }
+extern "C" const char *ffemb_version(void) { return "0.2.0"; }
 extern "C" int ffemb_compiled_sm(void) { return 100; }
 extern "C" int64_t ffemb_kernel_launch_count(void) { return g_launches.load(); }
 

@@ -105,3 +105,40 @@ def test_own_sort_ragged_bags_and_invalid_indices(K, impl):
         np.testing.assert_allclose(x.cpu().numpy(), y.cpu().numpy(), rtol=1e-5, atol=1e-5)
     c, _ = _step(K, impl, Ws, idxs, g, 21, 512)
     assert all(torch.equal(x, y) for x, y in zip(b, c))       # and it repeats itself exactly
+
+
+def test_wide_key_path_matches_the_oracle(K, oracle):
+    """Launch groups whose tables hold 2^32-1 rows or more in all use 64-bit keys
+    (make_keys<u64>, the library sort on u64, reduce_kernel<u64>).  Two tables
+    DECLARED with 2^31 + k rows (backed by small allocations; the indices stay
+    inside them) take that path; one index is out of range so that the
+    all-ones invalid key is sorted and skipped too."""
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(21)
+    D, B, L, real = 32, 700, 2, 3000
+    declared = [(1 << 31) + 5, (1 << 31) + 9]
+    Ws = [torch.randn(real, D, device="cuda", generator=gen) for _ in declared]
+    idx = [torch.randint(0, real, (B, L), device="cuda", generator=gen) for _ in declared]
+    idx[0][:50] = 7                                   # a long run
+    idx[1][3, 1] = declared[1]                        # out of range even for the declared size
+    g = torch.randn(B, 2 * D, device="cuda", generator=gen)
+    W0 = [w.cpu().numpy().copy() for w in Ws]
+    lk = K.make_lookups(Ws, idx)
+    for t, n in enumerate(declared):
+        lk[t].num_entries = n
+    ws = K.alloc_workspace(2 * B * L, sum(declared), D)
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    K.embed_backward_sgd(lk, B, D, 21, g, 0.05, ws, err)
+    torch.cuda.synchronize()
+    assert int(err.item()) == 3                       # FFEMB_ERR_INDEX_OUT_OF_RANGE, flagged not applied
+    g_h = g.cpu().numpy()
+    for t in range(2):
+        i_h = idx[t].cpu().numpy().copy()
+        gt = np.ascontiguousarray(g_h[:, t * D:(t + 1) * D]).copy()
+        if t == 1:                                    # the oracle refuses bad indices: drop that lookup's share
+            i_h[3, 1] = 0
+            want_fix = gt[3].copy()
+        _, want = oracle.step(W0[t], i_h, gt, 0.05)
+        if t == 1:
+            want[0] += np.float32(0.05) * want_fix    # undo the stand-in lookup of row 0
+        np.testing.assert_allclose(Ws[t].cpu().numpy(), want, rtol=1e-5, atol=2e-5)

@@ -92,7 +92,7 @@ def test_header_binds_with_cffi_like_the_reference_does():
     ffi = cffi.FFI()
     ffi.cdef(src[src.index("enum AggrMode"):])
     lib = ffi.dlopen(ff.library_path())
-    assert ffi.string(lib.ffemb_version()) == b"0.1.0" and lib.AGGR_MODE_SUM == 21 and lib.DT_INT64 == 43
+    assert ffi.string(lib.ffemb_version()) == b"0.2.0" and lib.AGGR_MODE_SUM == 21 and lib.DT_INT64 == 43
     s = lib.ffemb_strategy_create()
     assert lib.ffemb_strategy_generate_dlrm_simple(s, 8, 16) == 0 and lib.ffemb_strategy_num_ops(s) == 19
     assert lib.ffemb_strategy_device_for_table(s, 11, ffi.NULL, 8) == 3
