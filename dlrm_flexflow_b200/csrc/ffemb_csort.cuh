@@ -10,9 +10,9 @@
 //
 //   pass k   stable LSD radix pass on digit k (<= 9 bits; a table takes only
 //            ceil(bits(N_t) / 9) passes):
-//     load     the CTA's slab, coalesced (pass 0: the int64 index stream with
-//              its range check; later passes: the previous pass's output,
-//              which is still in L2; a one-CTA cluster just swaps buffers)
+//     load     pass 0 only: the CTA's slab of the int64 index stream, coalesced,
+//              with its range check (later passes find their slab in shared
+//              memory, where the previous pass left it)
 //     count    per-warp digit histograms (packed shared-memory atomics)
 //     barrier  cluster-wide; every CTA reads the other CTAs' digit totals
 //              through distributed shared memory and derives, per digit, its
@@ -21,17 +21,21 @@
 //              (= position order; the lanes of a row that share a digit find
 //              each other with one ballot per digit bit), scatter inside the
 //              CTA's OWN shared memory so that every digit's keys sit together
-//     copy     each digit's run goes to its slots with coalesced stores (the
-//              last pass writes global keys row_base + row and values)
+//     barrier  cluster-wide: every CTA is done reading its slab
+//     copy     each digit's run goes to the slab of the CTA that owns its slots:
+//              consecutive lanes hold consecutive slots of a run, so these
+//              are coalesced distributed-shared-memory stores (the last pass
+//              writes global keys row_base + row and values to memory)
 //     barrier  cluster-wide
 //
-// Elements move between CTAs only as coalesced runs through L2: scattered
-// 4-byte stores into another CTA's shared memory cost a packet each (measured:
-// 170 us for the MLPerf-Terabyte step done that way), whereas the digit totals
-// -- 2 KB per CTA and pass -- are what distributed shared memory is good at.
-// Against the multi-launch sorts (7-10 dependent launches, latency-bound on
-// 1.7 M keys) this is one launch of about 100 CTAs.  Tables whose segments do
-// not fit fall back to the global segmented sort of ffemb_sort.cuh.
+// Elements cross CTAs only as coalesced runs: scattering single 4-byte
+// elements into another CTA's shared memory costs a packet each (measured: 170
+// us for the MLPerf-Terabyte step done that way, against 80 us now).  Against
+// the multi-launch sorts (7-10 dependent launches, latency-bound on 1.7 M
+// keys) this is one launch of about 100 CTAs that reads the indices once and
+// writes nothing but the result.  A launch with few tables spreads each over
+// up to 8 CTAs (the sort is latency-bound per CTA); tiny segments stay in one.
+// Tables whose segments do not fit fall back to the library sort.
 #pragma once
 
 #include <cooperative_groups.h>
@@ -438,7 +442,7 @@ inline int cluster_sort_group(const ffemb_lookup_t *lookups, int T, int batch, u
   // latency-bound per CTA), a GPU that sorts 26 wants no more CTAs than needed.
   int C = 1;
   while ((int64_t)C * kCsSlab < max_n) C *= 2;
-  while (C < 8 && T * C * 2 <= 64) C *= 2;
+  while (C < 8 && T * C * 2 <= 64 && max_n >= (int64_t)C * 2 * 2048) C *= 2;  // slabs of 2048 slots or more
   int slab_log2 = 5;
   while (((int64_t)C << slab_log2) < max_n) ++slab_log2;
   cp.slab_log2 = slab_log2;
