@@ -16,10 +16,10 @@ if [ "$N" = "1" ]; then
   run c3_zipf1.05 --dist zipf --alpha 1.05 $FAST
 else
   run c3 --steps 50 --warmup 10 --no-cpu-baseline
-  if [ "$N" = "8" ]; then
-    run c3_plan --placement plan $FAST
-    run c4 --config C4 $FAST
-    run c5_zipf0 --config C5 --dist zipf --alpha 0 $FAST
-    run c5_zipf1.2 --config C5 --dist zipf --alpha 1.2 $FAST
-  fi
+  run c3_plan --placement plan $FAST
+  run c3_noreplicas --replicate off $FAST
+  run c4 --config C4 $FAST
+  # BASELINE.json config 5: the Zipf sweep at every N (FULL=1 for all five alphas)
+  if [ "$FULL" = "1" ]; then ALPHAS="0 0.4 0.8 1.0 1.2"; else ALPHAS="0 1.2"; fi
+  for a in $ALPHAS; do run c5_zipf$a --config C5 --dist zipf --alpha $a $FAST; done
 fi
