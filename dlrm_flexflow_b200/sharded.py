@@ -149,6 +149,10 @@ class ShardedEmbeddingBags(object):
                              update to this rank's tables.
     rep_indices              [B/N, bag] indices of this rank's own samples for
                              the replicated tables (plan.replicated), if any.
+
+    With one rank, forward() already sorts the keys of the coming backward; the
+    sort is reused when backward_update() gets the same index tensors (compared
+    by address), so do not modify them in between -- or pass presort=False.
     """
 
     def __init__(self, plan, rank, bag, aggr, lr, exchange="nccl", group=None, init_seed=1234, presort=True):
