@@ -137,7 +137,7 @@ class FFConfig(_Owned):
         check(lib().ffemb_config_set_replicate_below(self.handle, -1 if rows == "auto" else int(rows)))
 
     def set_gradient_exchange(self, mode):
-        """'auto' (pull with two ranks, push from three up), 'push' or 'pull'."""
+        """'auto' (pull with two ranks and one-hot bags, push otherwise), 'push' or 'pull'."""
         check(lib().ffemb_config_set_gradient_exchange(self.handle, {"auto": 0, "push": 1, "pull": 2}[mode]))
 
     def set_exchange_engine(self, force=True):

@@ -322,8 +322,9 @@ int ffemb_config_set_replicate_below(ffemb_config_t handle, int64_t rows);
  * matrix and the update reads local memory; 2 pull: the update kernel loads
  * gradient rows straight from the producing ranks' matrices (no staging
  * pass, but remote loads reach roughly half the NVLink rate of remote
- * stores); 0 (default): pull with two ranks, push from three up -- where each
- * measured faster. */
+ * stores); 0 (default): pull with two ranks and one-hot bags, push otherwise --
+ * where each measured faster (with bags of L lookups a pull would fetch every
+ * remote gradient row L times). */
 int ffemb_config_set_gradient_exchange(ffemb_config_t handle, int mode);
 /* Run the sharded engine (exchange buffer, barriers, staging) even with one
  * rank.  For tests on a single GPU. */
